@@ -1,0 +1,436 @@
+// H3 — GAE over packed variable-length sequences.
+//
+// Replaces csrc/cugae/gae.cu:10-60 of the reference (one *thread* per sequence, serial and
+// uncoalesced: 256 sequences occupy one CTA on one SM). Two kernels:
+//
+//  gae_serial_kernel  one warp per sequence. Loads/stores are warp-coalesced; the recurrence
+//                     itself is evaluated by one lane in exactly the reference's order with
+//                     the reference's fp32 contractions, so results are bit-identical to
+//                     gae_kernel_1d_nolp_misalign. Used when gamma*lam ~ 1, where any
+//                     re-association of the fp32 suffix sum moves results by more than the
+//                     1e-5 parity bar (the sum has no forgetting, errors random-walk).
+//
+//  gae_scan_kernel    the packed token stream is cut into fixed tiles of 1024 tokens, one warp
+//                     per tile, whatever the sequence lengths are (perfect balance: a 16k-token
+//                     sequence is spread over 16 warps, 16 sequences of 64 tokens share one).
+//                     Inside a tile: segmented reverse affine scan
+//                         (a1,b1) o (a2,b2) = (a1*a2, b1 + a1*b2),  a_t = gamma*lam (0 at a
+//                     sequence's last token), b_t = delta_t. Across tiles: single-pass decoupled
+//                     look-back on 64-bit {flag,value} words (tile g needs adv at the first
+//                     token of tile g+1; tiles take tickets right-to-left so a tile only ever
+//                     waits on tiles that already run).
+//
+// Bound: HBM. Algorithmic bytes: 16 B per token (r, v read; adv, ret written) + 9 B/sequence.
+#include "common.cuh"
+
+namespace b200rl {
+namespace {
+
+// ============================ SERIAL =========================================
+constexpr int kSerWarps = 4;
+constexpr int kSerBlk = 128;  // tokens per warp iteration
+
+__global__ void __launch_bounds__(kSerWarps * 32)
+gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+                  const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot,
+                  float* __restrict__ adv, float* __restrict__ ret, int batch, float gamma,
+                  float lam) {
+  __shared__ __align__(16) float sm[kSerWarps][kSerBlk];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float* d = sm[w];
+  const float c = __fmul_rn(gamma, lam);  // ref gae.cu:24 `gamma * lmbda * lastgae`
+  const int nwarps = gridDim.x * kSerWarps;
+  for (int i = blockIdx.x * kSerWarps + w; i < batch; i += nwarps) {
+    const int rs = cu[i], re = cu[i + 1];
+    const int n = re - rs;
+    if (n <= 0) continue;
+    const int64_t vs = (int64_t)rs + i;
+    const bool bs = boot[i] != 0;
+    float X = 0.f;  // lastgae
+    // software prefetch of the first block
+    float r[4], v[4], vn[4];
+    int hi = n;
+    int lo = max(hi - kSerBlk, 0);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      int u = lo + 32 * k + lane;
+      bool ok = u < hi;
+      r[k] = ok ? rewards[rs + u] : 0.f;
+      v[k] = ok ? values[vs + u] : 0.f;
+      vn[k] = ok ? values[vs + u + 1] : 0.f;
+    }
+    while (hi > 0) {
+      const int cnt = hi - lo;
+      // delta in the reference's contraction: fma(gamma, next_v, r) - v   (gae.cu:22-23)
+      float vk[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        int u = lo + 32 * k + lane;
+        float nv = (u == n - 1 && !bs) ? 0.f : vn[k];
+        float dl = __fsub_rn(__fmaf_rn(gamma, nv, r[k]), v[k]);
+        if (u < hi) d[32 * k + lane] = dl;
+        vk[k] = v[k];
+      }
+      // prefetch next block (to the left) while the chain runs
+      const int nhi = lo, nlo = max(lo - kSerBlk, 0);
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        int u = nlo + 32 * k + lane;
+        bool ok = u < nhi;
+        r[k] = ok ? rewards[rs + u] : 0.f;
+        v[k] = ok ? values[vs + u] : 0.f;
+        vn[k] = ok ? values[vs + u + 1] : 0.f;
+      }
+      __syncwarp();
+      if (lane == 0) {
+        int q = cnt - 1;
+        // tail down to a multiple of 4, then 4 at a time with 16-B smem accesses
+        for (; (q & 3) != 3 && q >= 0; q--) {
+          X = __fmaf_rn(c, X, d[q]);
+          d[q] = X;
+        }
+        for (; q >= 3; q -= 4) {
+          float4 t = *reinterpret_cast<float4*>(d + q - 3);
+          t.w = X = __fmaf_rn(c, X, t.w);
+          t.z = X = __fmaf_rn(c, X, t.z);
+          t.y = X = __fmaf_rn(c, X, t.y);
+          t.x = X = __fmaf_rn(c, X, t.x);
+          *reinterpret_cast<float4*>(d + q - 3) = t;
+        }
+      }
+      __syncwarp();
+      X = __shfl_sync(0xffffffffu, X, 0);
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        int u = lo + 32 * k + lane;
+        if (u < hi) {
+          float A = d[32 * k + lane];
+          adv[rs + u] = A;
+          ret[rs + u] = __fadd_rn(A, vk[k]);  // gae.cu:26
+        }
+      }
+      __syncwarp();
+      hi = nhi;
+      lo = nlo;
+    }
+  }
+}
+
+// ============================ SCAN ===========================================
+constexpr int kTile = 1024;   // tokens per warp tile
+constexpr int kBlk = 128;     // tokens per scan step (32 lanes x 4)
+constexpr int kScanWarps = 4;
+constexpr uint32_t kFlagAgg = 1u, kFlagIncl = 2u;
+constexpr int kMetaLast = 1 << 30;
+constexpr int kMetaBoot = 1 << 29;
+constexpr int kMetaCnt = (1 << 24) - 1;
+
+struct ScanSmem {
+  float d[kTile];    // delta, then adv (zero carry-in)
+  float v[kTile];    // value of the token
+  int meta[kTile];   // start-count / relative sequence id, LAST/BOOT flags
+};
+
+__device__ __forceinline__ uint64_t ld_state(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_state(uint64_t* p, uint32_t flag, float val) {
+  uint64_t v = ((uint64_t)flag << 32) | (uint64_t)__float_as_uint(val);
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// #{k in [1, batch] : cu[k] <= x}, warp-cooperative 32-ary search (all lanes return it)
+__device__ __forceinline__ int count_ends_le(const int32_t* __restrict__ cu, int batch, int x,
+                                             int lane) {
+  int lo = 1, hi = batch + 1;  // predicate true for k < lo, false for k >= hi
+  while (lo < hi) {
+    const int width = hi - lo;
+    const int step = (width + 31) >> 5;
+    int k = lo + (lane + 1) * step - 1;
+    if (k > hi - 1) k = hi - 1;
+    const bool pred = cu[k] <= x;
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    const int nt = __popc(m);  // predicate is monotone: the first nt lanes are true
+    if (nt == 32) {
+      lo = hi;  // last probe is hi-1 (clamped) and true
+    } else {
+      int kf = lo + (nt + 1) * step - 1;  // first false probe
+      if (kf > hi - 1) kf = hi - 1;
+      const int new_lo = nt ? min(lo + nt * step, hi) : lo;
+      hi = kf;
+      lo = new_lo;
+    }
+  }
+  return lo - 1;
+}
+
+__global__ void __launch_bounds__(kScanWarps * 32)
+gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+                const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot,
+                float* __restrict__ adv, float* __restrict__ ret, int batch, int total,
+                float gamma, float lam, uint64_t* __restrict__ state,
+                unsigned int* __restrict__ ticket_ctr, int num_tiles) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  ScanSmem& S = reinterpret_cast<ScanSmem*>(smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const float c = gamma * lam;
+  const float lc = log2f(c);        // -inf when c == 0: powers below become exact zeros
+  const float c2 = c * c, c3 = c2 * c, c4 = c2 * c2;
+  (void)c4;
+
+  while (true) {
+    unsigned int ticket = 0;
+    if (lane == 0) ticket = atomicAdd(ticket_ctr, 1u);
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket >= (unsigned)num_tiles) break;
+    const int g = num_tiles - 1 - (int)ticket;  // right-most tile first
+    const int tlo = g * kTile;
+    const int thi = min(tlo + kTile, total);
+    const int tlen = thi - tlo;
+
+    // ---- prologue: sequence ids and flags of the tile's tokens --------------------------
+    const int i_lo = count_ends_le(cu, batch, tlo, lane);  // sequence that owns token tlo
+#pragma unroll
+    for (int k = 0; k < kTile / 128; k++)
+      *reinterpret_cast<int4*>(&S.meta[k * 128 + lane * 4]) = make_int4(0, 0, 0, 0);
+    __syncwarp();
+    for (int base = i_lo;; base += 32) {
+      const int i = base + lane;
+      bool more = false;
+      if (i < batch) {
+        const int s = cu[i], e = cu[i + 1];
+        if (i > i_lo && s < thi) atomicAdd(&S.meta[s - tlo], 1);  // a sequence starts here
+        if (e > s && e - 1 >= tlo && e - 1 < thi)
+          atomicOr(&S.meta[e - 1 - tlo], kMetaLast | (boot[i] ? kMetaBoot : 0));
+        more = e < thi;  // sequences after this one may still start inside the tile
+      }
+      if (__ballot_sync(0xffffffffu, more) != 0xffffffffu) break;
+    }
+    __syncwarp();
+    // inclusive prefix sum of the start counts -> relative sequence id per token
+    {
+      int run = 0;
+#pragma unroll 1
+      for (int k = 0; k < kTile / 128; k++) {
+        int4 m = *reinterpret_cast<int4*>(&S.meta[k * 128 + lane * 4]);
+        int c0 = m.x & kMetaCnt, c1 = m.y & kMetaCnt, c2_ = m.z & kMetaCnt, c3_ = m.w & kMetaCnt;
+        int s0 = c0, s1 = s0 + c1, s2 = s1 + c2_, s3 = s2 + c3_;
+        int inc = s3;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          int t = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += t;
+        }
+        const int ex = run + inc - s3;
+        m.x = (m.x & ~kMetaCnt) | (ex + s0);
+        m.y = (m.y & ~kMetaCnt) | (ex + s1);
+        m.z = (m.z & ~kMetaCnt) | (ex + s2);
+        m.w = (m.w & ~kMetaCnt) | (ex + s3);
+        *reinterpret_cast<int4*>(&S.meta[k * 128 + lane * 4]) = m;
+        run += __shfl_sync(0xffffffffu, inc, 31);
+      }
+    }
+    __syncwarp();
+
+    // ---- load (coalesced, lane-strided) and delta ---------------------------------------
+#pragma unroll 2
+    for (int k = 0; k < kTile / 32; k++) {
+      const int o = k * 32 + lane;
+      if (o < tlen) {
+        const int t = tlo + o;
+        const int m = S.meta[o];
+        const int64_t vi = (int64_t)t + i_lo + (m & kMetaCnt);
+        const float r = rewards[t];
+        const float v = values[vi];
+        float nv = values[vi + 1];
+        if ((m & kMetaLast) && !(m & kMetaBoot)) nv = 0.f;
+        S.d[o] = fmaf(gamma, nv, r) - v;
+        S.v[o] = v;
+      } else {
+        S.d[o] = 0.f;
+        S.meta[o] = 0;
+      }
+    }
+    __syncwarp();
+
+    // ---- segmented reverse scan with zero carry-in at the tile's right edge --------------
+    int last_boundary = -1;  // tile-local index of the right-most LAST token
+    float X = 0.f;           // adv of the first token of the block to the right (carry)
+#pragma unroll 1
+    for (int blk = kTile / kBlk - 1; blk >= 0; blk--) {
+      const int o = blk * kBlk + lane * 4;
+      float4 dl = *reinterpret_cast<float4*>(&S.d[o]);
+      int4 m = *reinterpret_cast<int4*>(&S.meta[o]);
+      const float a0 = (m.x & kMetaLast) ? 0.f : c, a1 = (m.y & kMetaLast) ? 0.f : c,
+                  a2 = (m.z & kMetaLast) ? 0.f : c, a3 = (m.w & kMetaLast) ? 0.f : c;
+      // lane-local: L_k = adv with zero carry, P_k = prod a_k..a_3
+      const float L3 = dl.w, P3 = a3;
+      const float L2 = fmaf(a2, L3, dl.z), P2 = a2 * P3;
+      const float L1 = fmaf(a1, L2, dl.y), P1 = a1 * P2;
+      const float L0 = fmaf(a0, L1, dl.x), P0 = a0 * P1;
+      // suffix (towards higher lanes) inclusive scan of (P0, L0)
+      float Q = P0, Sx = L0;
+#pragma unroll
+      for (int sft = 1; sft < 32; sft <<= 1) {
+        const float q2 = __shfl_down_sync(0xffffffffu, Q, sft);
+        const float s2 = __shfl_down_sync(0xffffffffu, Sx, sft);
+        if (lane + sft < 32) {
+          Sx = fmaf(Q, s2, Sx);
+          Q = Q * q2;
+        }
+      }
+      // composite of the lanes to my right, applied to the block carry X
+      float Qr = __shfl_down_sync(0xffffffffu, Q, 1);
+      float Sr = __shfl_down_sync(0xffffffffu, Sx, 1);
+      if (lane == 31) {
+        Qr = 1.f;
+        Sr = 0.f;
+      }
+      const float carry = fmaf(Qr, X, Sr);
+      float4 A;
+      A.w = fmaf(P3, carry, L3);
+      A.z = fmaf(P2, carry, L2);
+      A.y = fmaf(P1, carry, L1);
+      A.x = fmaf(P0, carry, L0);
+      *reinterpret_cast<float4*>(&S.d[o]) = A;
+      X = __shfl_sync(0xffffffffu, A.x, 0);
+      if (last_boundary < 0) {
+        const unsigned lm = ((m.x & kMetaLast) ? 1u : 0u) | ((m.y & kMetaLast) ? 2u : 0u) |
+                            ((m.z & kMetaLast) ? 4u : 0u) | ((m.w & kMetaLast) ? 8u : 0u);
+        const unsigned any = __ballot_sync(0xffffffffu, lm != 0);
+        if (any) {
+          const int hl = 31 - __clz(any);  // highest lane with a boundary
+          const unsigned hm = __shfl_sync(0xffffffffu, lm, hl);
+          last_boundary = blk * kBlk + hl * 4 + (31 - __clz(hm));
+        }
+      }
+    }
+    const float first_zero_carry = X;  // adv of token tlo assuming zero carry-in
+
+    // ---- publish / look back -------------------------------------------------------------
+    const bool need_carry = thi < total && last_boundary != tlen - 1;
+    const bool closed = last_boundary >= 0;  // first token's adv does not depend on the carry
+    if (lane == 0 && g > 0) {
+      if (closed || !need_carry) st_state(&state[g], kFlagIncl, first_zero_carry);
+      else st_state(&state[g], kFlagAgg, first_zero_carry);
+    }
+    float Xin = 0.f;
+    if (need_carry) {
+      if (lane == 0) {
+        const float cT = exp2f(lc * (float)kTile);
+        float mult = 1.f;
+        int j = g + 1;
+        while (true) {
+          uint64_t st;
+          while (((st = ld_state(&state[j])) >> 32) == 0) __nanosleep(32);
+          Xin = fmaf(mult, __uint_as_float((uint32_t)st), Xin);
+          if ((uint32_t)(st >> 32) == kFlagIncl) break;
+          mult *= cT;
+          j++;
+        }
+        if (!closed && g > 0)
+          st_state(&state[g], kFlagIncl, fmaf(exp2f(lc * (float)tlen), Xin, first_zero_carry));
+      }
+      Xin = __shfl_sync(0xffffffffu, Xin, 0);
+    }
+
+    // ---- write back (coalesced); tokens right of the last boundary take the carry -----------
+#pragma unroll 2
+    for (int k = 0; k < kTile / 32; k++) {
+      const int o = k * 32 + lane;
+      if (o < tlen) {
+        float A = S.d[o];
+        if (need_carry && o > last_boundary) A = fmaf(exp2f(lc * (float)(tlen - o)), Xin, A);
+        adv[tlo + o] = A;
+        ret[tlo + o] = A + S.v[o];
+      }
+    }
+    __syncwarp();
+    (void)c2; (void)c3;
+  }
+}
+
+struct ScanWs {
+  unsigned int* ticket;
+  uint64_t* state;
+  int num_tiles;
+  size_t bytes;
+};
+ScanWs scan_ws(void* ws, int64_t total) {
+  ScanWs W;
+  W.num_tiles = (int)((total + kTile - 1) / kTile);
+  W.ticket = (unsigned int*)ws;
+  W.state = (uint64_t*)((char*)ws + 256);
+  W.bytes = 256 + (size_t)(W.num_tiles + 1) * sizeof(uint64_t);
+  W.bytes = (W.bytes + 255) & ~(size_t)255;
+  return W;
+}
+
+}  // namespace
+}  // namespace b200rl
+
+extern "C" {
+
+size_t b200rl_gae_workspace_bytes(int32_t batch, int64_t total) {
+  (void)batch;
+  if (total < 0) return 0;
+  return b200rl::scan_ws(nullptr, total).bytes;
+}
+
+int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
+                                const int32_t* cu_seqlens, const uint8_t* bootstrap, float* adv,
+                                float* ret, int32_t batch, int64_t total, float gamma, float lam,
+                                int mode, void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace b200rl;
+  B200RL_REQUIRE(batch >= 0 && total >= 0, "negative size");
+  B200RL_REQUIRE(total < (int64_t)INT32_MAX - batch, "total tokens must fit int32 (cu_seqlens is int32)");
+  if (batch == 0 || total == 0) return B200RL_OK;
+  B200RL_REQUIRE(rewards && values && cu_seqlens && bootstrap && adv && ret, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == B200RL_GAE_AUTO) {
+    // SCAN re-associates fp32 additions; its deviation from the serial order stays below the
+    // 1e-5 bar only while gamma*lam forgets fast enough (measured: tests/test_gae.py).
+    const float c = gamma * lam;
+    mode = (c > 0.99f || !(c >= 0.f)) ? B200RL_GAE_SERIAL : B200RL_GAE_SCAN;
+  }
+  if (mode == B200RL_GAE_SERIAL) {
+    int grid = (batch + kSerWarps - 1) / kSerWarps;
+    const int cap = sm_count() * 16;
+    if (grid > cap) grid = cap;
+    gae_serial_kernel<<<grid, kSerWarps * 32, 0, st>>>(rewards, values, cu_seqlens, bootstrap, adv,
+                                                      ret, batch, gamma, lam);
+    return check_launch("gae_serial_kernel");
+  }
+  if (mode == B200RL_GAE_SCAN) {
+    B200RL_REQUIRE(workspace != nullptr, "SCAN mode needs a workspace");
+    B200RL_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "workspace must be 256-B aligned");
+    ScanWs W = scan_ws(workspace, total);
+    if (workspace_bytes < W.bytes) {
+      set_last_error("gae workspace too small: %zu < %zu", workspace_bytes, W.bytes);
+      return B200RL_EWORKSPACE;
+    }
+    B200RL_CUDA(cudaMemsetAsync(workspace, 0, W.bytes, st));
+    static bool attr_set[64] = {false};
+    const size_t smem = sizeof(ScanSmem) * kScanWarps;
+    int dev = 0;
+    B200RL_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      B200RL_CUDA(cudaFuncSetAttribute(gae_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+      attr_set[dev] = true;
+    }
+    int grid = (W.num_tiles + kScanWarps - 1) / kScanWarps;
+    const int cap = sm_count() * 4;  // 4 CTAs x 4 warps x 12 KiB = 192 KiB smem per SM
+    if (grid > cap) grid = cap;
+    gae_scan_kernel<<<grid, kScanWarps * 32, smem, st>>>(rewards, values, cu_seqlens, bootstrap,
+                                                        adv, ret, batch, (int)total, gamma, lam,
+                                                        W.state, W.ticket, W.num_tiles);
+    return check_launch("gae_scan_kernel");
+  }
+  set_last_error("unknown GAE mode %d", mode);
+  return B200RL_EINVAL;
+}
+
+}  // extern "C"

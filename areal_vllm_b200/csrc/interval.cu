@@ -1,0 +1,377 @@
+// H4 — interval gather/scatter on a flat parameter buffer (weight resharding).
+//
+// Replaces csrc/interval_op/interval_op.cu:12-114 of the reference, whose copyDataKernel gives
+// every *thread* a serial <=4 KiB memcpy of its own interval chunk (uncoalesced, grid sized by
+// the largest interval). Here the PACKED side of the copy is cut into fixed 16 KiB tiles, one
+// warp per tile, so the launch is balanced whatever the interval-size skew is; inside a tile the
+// warp walks the intervals that overlap it and moves each piece with 16-byte vector accesses
+// aligned on the store side (narrower vectors when source and destination are mutually
+// misaligned). The per-interval packed offsets (exclusive prefix sum of the lengths, which the
+// reference builds with three aten ops per call, interval_op.cu:49-51,84-86) and the
+// tile -> first-interval map form a "plan" kept in caller-owned workspace and reusable across
+// calls with the same interval list.
+//
+// Bound: HBM. Algorithmic bytes = 2 * elem_size per copied element (+16 B per interval).
+#include "common.cuh"
+
+namespace b200rl {
+namespace {
+
+constexpr int kTileBytes = 16384;     // packed bytes per warp tile
+constexpr int kCopyWarps = 8;         // warps per CTA in the copy kernel
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;         // intervals per thread in the local scan
+constexpr int kScanBlock = kScanThreads * kScanItems;  // 2048 intervals per CTA
+
+struct PlanLayout {
+  int64_t* hdr;         // [0] total elems, [1] error flag, [2] n, [3] packed_numel
+  int64_t* offsets;     // [n+1]
+  int64_t* block_sums;  // [nb]
+  int32_t* tile_first;  // [num_tiles+1]
+  int64_t nb, num_tiles;
+  size_t bytes;
+};
+
+__host__ PlanLayout plan_layout(void* ws, int64_t n, int64_t packed_numel, int elem_size) {
+  PlanLayout L;
+  L.nb = (n + kScanBlock - 1) / kScanBlock;
+  if (L.nb < 1) L.nb = 1;
+  int64_t packed_bytes = packed_numel * (int64_t)elem_size;
+  L.num_tiles = (packed_bytes + kTileBytes - 1) / kTileBytes;
+  char* p = (char*)ws;
+  size_t off = 0;
+  L.hdr = (int64_t*)(p + off);
+  off += 4 * sizeof(int64_t);
+  L.offsets = (int64_t*)(p + off);
+  off += (size_t)(n + 1) * sizeof(int64_t);
+  L.block_sums = (int64_t*)(p + off);
+  off += (size_t)L.nb * sizeof(int64_t);
+  L.tile_first = (int32_t*)(p + off);
+  off += (size_t)(L.num_tiles + 1) * sizeof(int32_t);
+  L.bytes = (off + 255) & ~(size_t)255;
+  return L;
+}
+
+// ---- plan kernels ----------------------------------------------------------
+// K1: lengths + validation + CTA-local exclusive scan.
+__global__ void __launch_bounds__(kScanThreads)
+interval_local_scan(const int64_t* __restrict__ intervals, int64_t n, int64_t big_numel,
+                    int64_t* __restrict__ offsets, int64_t* __restrict__ block_sums,
+                    int64_t* __restrict__ hdr) {
+  __shared__ int64_t warp_tot[kScanThreads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t base = (int64_t)blockIdx.x * kScanBlock + (int64_t)tid * kScanItems;
+  int64_t len[kScanItems];
+  int64_t tsum = 0;
+  bool bad = false;
+#pragma unroll
+  for (int k = 0; k < kScanItems; k++) {
+    int64_t i = base + k;
+    int64_t l = 0;
+    if (i < n) {
+      // one 16-B load per interval: {start, end}
+      longlong2 se = *reinterpret_cast<const longlong2*>(intervals + 2 * i);
+      l = se.y - se.x;
+      if (se.x < 0 || l < 0 || se.y > big_numel) {
+        bad = true;
+        l = 0;  // malformed intervals copy nothing
+      }
+    }
+    len[k] = l;
+    tsum += l;
+  }
+  // warp inclusive scan of per-thread sums
+  int64_t inc = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int64_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) warp_tot[warp] = inc;
+  __syncthreads();
+  int64_t wbase = 0;
+#pragma unroll
+  for (int w = 0; w < kScanThreads / 32; w++)
+    if (w < warp) wbase += warp_tot[w];
+  int64_t run = wbase + inc - tsum;
+#pragma unroll
+  for (int k = 0; k < kScanItems; k++) {
+    int64_t i = base + k;
+    if (i < n) offsets[i] = run;
+    run += len[k];
+  }
+  if (tid == kScanThreads - 1) block_sums[blockIdx.x] = run;
+  if (bad) hdr[1] = 1;
+}
+
+// K2: exclusive scan of the per-CTA sums (single CTA) + header.
+__global__ void __launch_bounds__(1024)
+interval_block_scan(int64_t* __restrict__ block_sums, int64_t nb, int64_t* __restrict__ hdr,
+                    int64_t n, int64_t packed_numel) {
+  __shared__ int64_t part[1024];
+  const int tid = threadIdx.x;
+  const int64_t per = (nb + 1023) / 1024;
+  const int64_t lo = tid * per, hi = min(lo + per, nb);
+  int64_t s = 0;
+  for (int64_t i = lo; i < hi; i++) s += block_sums[i];
+  part[tid] = s;
+  __syncthreads();
+  // Hillis-Steele over 1024 partials
+  for (int o = 1; o < 1024; o <<= 1) {
+    int64_t v = (tid >= o) ? part[tid - o] : 0;
+    __syncthreads();
+    part[tid] += v;
+    __syncthreads();
+  }
+  int64_t run = part[tid] - s;
+  for (int64_t i = lo; i < hi; i++) {
+    int64_t v = block_sums[i];
+    block_sums[i] = run;
+    run += v;
+  }
+  if (tid == 1023) {
+    hdr[0] = part[1023];
+    hdr[2] = n;
+    hdr[3] = packed_numel;
+    if (part[1023] != packed_numel) hdr[1] |= 2;  // sum of lengths != packed size
+  }
+}
+
+// K3: add the CTA base, write offsets[n] = total.
+__global__ void __launch_bounds__(256)
+interval_add_base(int64_t* __restrict__ offsets, const int64_t* __restrict__ block_sums,
+                  const int64_t* __restrict__ hdr, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i < n) offsets[i] += block_sums[i / kScanBlock];
+  if (i == n) offsets[n] = hdr[0];
+}
+
+// K4: tile_first[t] = last interval whose packed offset is <= the tile's first element
+// (upper_bound - 1, which skips empty intervals).
+__global__ void __launch_bounds__(256)
+interval_partition(const int64_t* __restrict__ offsets, int64_t n, int32_t* __restrict__ tile_first,
+                   int64_t num_tiles, int elem_shift) {
+  int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t > num_tiles) return;
+  if (t == num_tiles) {
+    tile_first[t] = (int32_t)n;
+    return;
+  }
+  const int64_t pos = (t * (int64_t)kTileBytes) >> elem_shift;  // first packed element of tile
+  int64_t lo = 0, hi = n + 1;  // upper_bound over offsets[0..n]
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (offsets[mid] <= pos) lo = mid + 1; else hi = mid;
+  }
+  int64_t idx = lo - 1;
+  if (idx < 0) idx = 0;
+  if (idx > n - 1) idx = n - 1;
+  tile_first[t] = (int32_t)idx;
+}
+
+// ---- copy ------------------------------------------------------------------
+template <int W> struct VecT;
+template <> struct VecT<16> { using type = uint4; };
+template <> struct VecT<8> { using type = uint2; };
+template <> struct VecT<4> { using type = uint32_t; };
+template <> struct VecT<2> { using type = uint16_t; };
+template <> struct VecT<1> { using type = uint8_t; };
+
+template <int W>
+__device__ __forceinline__ typename VecT<W>::type ld_stream(const char* p) {
+  if constexpr (W == 16) {
+    return ldg_nc_v4(p);
+  } else {
+    return __ldg(reinterpret_cast<const typename VecT<W>::type*>(p));
+  }
+}
+template <int W>
+__device__ __forceinline__ void st_stream(char* p, typename VecT<W>::type v) {
+  if constexpr (W == 16) {
+    stg_na_v4(p, v);
+  } else {
+    *reinterpret_cast<typename VecT<W>::type*>(p) = v;
+  }
+}
+
+// element-granular copy of `bytes` (< 32*ES*k small) by the warp
+template <int ES>
+__device__ __forceinline__ void copy_small(const char* s, char* d, int bytes, int lane) {
+  for (int o = lane * ES; o < bytes; o += 32 * ES) st_stream<ES>(d + o, ld_stream<ES>(s + o));
+}
+
+// Warp-cooperative copy of `bytes` from s to d using W-byte accesses on the body.
+// Requires (s - d) % W == 0 and ES | W; d, s are ES-aligned.
+template <int W, int ES>
+__device__ __forceinline__ void copy_piece_w(const char* s, char* d, int64_t bytes, int lane) {
+  if constexpr (W > ES) {
+    int head = (int)((W - (reinterpret_cast<uintptr_t>(d) & (W - 1))) & (W - 1));
+    if (head > bytes) head = (int)bytes;
+    copy_small<ES>(s, d, head, lane);
+    s += head;
+    d += head;
+    bytes -= head;
+  }
+  const int64_t nv = bytes / W;
+  constexpr int U = 4;
+  int64_t v = lane;
+  for (; v + 32 * (U - 1) < nv; v += 32 * U) {
+    typename VecT<W>::type r[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) r[u] = ld_stream<W>(s + (v + 32 * u) * W);
+#pragma unroll
+    for (int u = 0; u < U; u++) st_stream<W>(d + (v + 32 * u) * W, r[u]);
+  }
+  for (; v < nv; v += 32) st_stream<W>(d + v * W, ld_stream<W>(s + v * W));
+  if constexpr (W > ES) {
+    int tail = (int)(bytes - nv * W);
+    copy_small<ES>(s + nv * W, d + nv * W, tail, lane);
+  }
+}
+
+template <int ES>
+__device__ __forceinline__ void copy_piece(const char* s, char* d, int64_t bytes, int lane) {
+  const unsigned rel = (unsigned)((reinterpret_cast<uintptr_t>(s) - reinterpret_cast<uintptr_t>(d)) & 15u);
+  if (rel == 0) {
+    copy_piece_w<16, ES>(s, d, bytes, lane);
+  } else if constexpr (ES < 8) {
+    if ((rel & 7u) == 0) {
+      copy_piece_w<8, ES>(s, d, bytes, lane);
+    } else if constexpr (ES < 4) {
+      if ((rel & 3u) == 0) {
+        copy_piece_w<4, ES>(s, d, bytes, lane);
+      } else if constexpr (ES < 2) {
+        if ((rel & 1u) == 0) copy_piece_w<2, ES>(s, d, bytes, lane);
+        else copy_piece_w<1, ES>(s, d, bytes, lane);
+      } else {
+        copy_piece_w<2, ES>(s, d, bytes, lane);
+      }
+    } else {
+      copy_piece_w<4, ES>(s, d, bytes, lane);
+    }
+  } else {
+    copy_piece_w<8, ES>(s, d, bytes, lane);
+  }
+}
+
+// MODE 0: slice (big -> packed).  MODE 1: set (packed -> big).
+template <int MODE, int ES>
+__global__ void __launch_bounds__(kCopyWarps * 32)
+interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
+                     const int64_t* __restrict__ intervals, const int64_t* __restrict__ offsets,
+                     const int32_t* __restrict__ tile_first, const int64_t* __restrict__ hdr,
+                     int64_t n, int64_t num_tiles) {
+  const int lane = threadIdx.x & 31;
+  const int64_t tile = (int64_t)blockIdx.x * kCopyWarps + (threadIdx.x >> 5);
+  if (tile >= num_tiles) return;
+  int64_t total_elems = hdr[0];
+  if (total_elems > hdr[3]) total_elems = hdr[3];  // never write past the packed buffer
+  const int64_t total_bytes = total_elems * ES;
+  int64_t p0 = tile * (int64_t)kTileBytes;
+  int64_t p1 = p0 + kTileBytes;
+  if (p1 > total_bytes) p1 = total_bytes;
+  int64_t i = tile_first[tile];
+  while (p0 < p1 && i < n) {
+    const int64_t ob = offsets[i] * ES;
+    const int64_t oe = offsets[i + 1] * ES;
+    if (oe <= p0) {  // empty interval (or one that ends before this tile)
+      i++;
+      continue;
+    }
+    const int64_t start = intervals[2 * i] * ES;
+    const int64_t b = oe < p1 ? oe : p1;
+    const int64_t big_off = start + (p0 - ob);
+    if (MODE == 0) copy_piece<ES>(src + big_off, dst + p0, b - p0, lane);
+    else           copy_piece<ES>(src + p0, dst + big_off, b - p0, lane);
+    p0 = b;
+    if (b == oe) i++;
+  }
+}
+
+int elem_shift_of(int elem_size) {
+  switch (elem_size) {
+    case 1: return 0;
+    case 2: return 1;
+    case 4: return 2;
+    case 8: return 3;
+    default: return -1;
+  }
+}
+
+int build_plan(const PlanLayout& L, const int64_t* intervals, int64_t n, int64_t big_numel,
+               int64_t packed_numel, int elem_shift, cudaStream_t st) {
+  B200RL_CUDA(cudaMemsetAsync(L.hdr, 0, 4 * sizeof(int64_t), st));
+  interval_local_scan<<<(unsigned)L.nb, kScanThreads, 0, st>>>(intervals, n, big_numel, L.offsets,
+                                                               L.block_sums, L.hdr);
+  interval_block_scan<<<1, 1024, 0, st>>>(L.block_sums, L.nb, L.hdr, n, packed_numel);
+  interval_add_base<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(L.offsets, L.block_sums, L.hdr, n);
+  interval_partition<<<(unsigned)((L.num_tiles + 1 + 255) / 256), 256, 0, st>>>(
+      L.offsets, n, L.tile_first, L.num_tiles, elem_shift);
+  return check_launch("interval plan");
+}
+
+template <int MODE>
+int run_copy(const void* src, void* dst, int64_t big_numel, int64_t packed_numel,
+             const int64_t* intervals, int64_t n, int elem_size, void* ws, size_t ws_bytes,
+             int reuse_plan, void* stream) {
+  B200RL_REQUIRE(n >= 0 && packed_numel >= 0 && big_numel >= 0, "negative size");
+  const int shift = elem_shift_of(elem_size);
+  B200RL_REQUIRE(shift >= 0, "elem_size %d not in {1,2,4,8}", elem_size);
+  if (n == 0 || packed_numel == 0) return B200RL_OK;
+  B200RL_REQUIRE(src && dst && intervals && ws, "null pointer");
+  B200RL_REQUIRE(n < (int64_t)INT32_MAX, "too many intervals");
+  B200RL_REQUIRE((reinterpret_cast<uintptr_t>(intervals) & 15) == 0, "intervals must be 16-B aligned");
+  B200RL_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "workspace must be 16-B aligned");
+  B200RL_REQUIRE(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & (elem_size - 1)) == 0,
+                 "src/dst must be element aligned");
+  PlanLayout L = plan_layout(ws, n, packed_numel, elem_size);
+  if (ws_bytes < L.bytes) {
+    set_last_error("interval workspace too small: %zu < %zu", ws_bytes, L.bytes);
+    return B200RL_EWORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!reuse_plan) {
+    int rc = build_plan(L, intervals, n, big_numel, packed_numel, shift, st);
+    if (rc) return rc;
+  }
+  const unsigned grid = (unsigned)((L.num_tiles + kCopyWarps - 1) / kCopyWarps);
+  const char* s = (const char*)src;
+  char* d = (char*)dst;
+#define LAUNCH(ES)                                                                             \
+  interval_copy_kernel<MODE, ES><<<grid, kCopyWarps * 32, 0, st>>>(s, d, intervals, L.offsets, \
+                                                                  L.tile_first, L.hdr, n, L.num_tiles)
+  switch (elem_size) {
+    case 1: LAUNCH(1); break;
+    case 2: LAUNCH(2); break;
+    case 4: LAUNCH(4); break;
+    default: LAUNCH(8); break;
+  }
+#undef LAUNCH
+  return check_launch("interval_copy_kernel");
+}
+
+}  // namespace
+}  // namespace b200rl
+
+extern "C" {
+
+size_t b200rl_interval_workspace_bytes(int64_t n_intervals, int64_t packed_numel, int elem_size) {
+  if (n_intervals < 0 || packed_numel < 0 || elem_size <= 0) return 0;
+  return b200rl::plan_layout(nullptr, n_intervals, packed_numel, elem_size).bytes;
+}
+
+int b200rl_slice_intervals(const void* big, int64_t big_numel, void* packed, int64_t packed_numel,
+                           const int64_t* intervals, int64_t n_intervals, int elem_size,
+                           void* workspace, size_t workspace_bytes, int reuse_plan, void* stream) {
+  return b200rl::run_copy<0>(big, packed, big_numel, packed_numel, intervals, n_intervals,
+                             elem_size, workspace, workspace_bytes, reuse_plan, stream);
+}
+
+int b200rl_set_intervals(const void* packed, int64_t packed_numel, void* big, int64_t big_numel,
+                         const int64_t* intervals, int64_t n_intervals, int elem_size,
+                         void* workspace, size_t workspace_bytes, int reuse_plan, void* stream) {
+  return b200rl::run_copy<1>(packed, big, big_numel, packed_numel, intervals, n_intervals,
+                             elem_size, workspace, workspace_bytes, reuse_plan, stream);
+}
+
+}  // extern "C"

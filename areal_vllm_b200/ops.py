@@ -1,0 +1,407 @@
+"""torch.library custom ops over the C ABI (the "thin torch custom-op layer").
+
+Each op validates, allocates outputs/workspace with torch (plumbing only) and launches exactly
+the C-ABI entry point on the current CUDA stream. Fake (meta) implementations are registered so
+the ops trace under torch.compile / CUDA-graph capture; none of them synchronises with the host.
+"""
+
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import check, lib, ptr, stream_handle
+
+Tensor = torch.Tensor
+
+
+# --------------------------------------------------------------------------------------------
+# H1 log-prob / entropy
+# --------------------------------------------------------------------------------------------
+def _check_logits(logits: Tensor, labels: Tensor) -> None:
+    _lib.require_cuda(logits=logits, labels=labels)
+    if logits.dim() != 2:
+        raise RuntimeError(f"logits must be [T, V], got {tuple(logits.shape)}")
+    if labels.dim() != 1 or labels.shape[0] != logits.shape[0]:
+        raise RuntimeError(f"labels must be [T]={logits.shape[0]}, got {tuple(labels.shape)}")
+    if labels.dtype != torch.int64:
+        raise RuntimeError(f"labels must be int64, got {labels.dtype}")
+    if logits.dtype not in _lib.DTYPE_CODE:
+        raise NotImplementedError(logits.dtype)
+    if logits.stride(1) != 1:
+        raise RuntimeError("logits rows must be contiguous (stride(-1) == 1)")
+    if not labels.is_contiguous():
+        raise RuntimeError("labels must be contiguous")
+
+
+@torch.library.custom_op("b200rl::logprob_entropy_fwd", mutates_args=())
+def logprob_entropy_fwd(
+    logits: Tensor, labels: Tensor, temperature: float, need_entropy: bool, need_minmax: bool
+) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """-> (logp[T], entropy[T] or empty, lse[T], rowmax[T] or empty, rowmin[T] or empty), all fp32."""
+    _check_logits(logits, labels)
+    T, V = logits.shape
+    dev = logits.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    logp = torch.empty(T, **f32)
+    lse = torch.empty(T, **f32)
+    ent = torch.empty(T if need_entropy else 0, **f32)
+    rmax = torch.empty(T if need_minmax else 0, **f32)
+    rmin = torch.empty(T if need_minmax else 0, **f32)
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_logprob_entropy_fwd(
+            ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
+            ptr(labels), T, V, float(temperature), ptr(logp),
+            ptr(ent) if need_entropy else None, ptr(lse),
+            ptr(rmax) if need_minmax else None, ptr(rmin) if need_minmax else None,
+            stream_handle(dev),
+        )
+    check(rc, "b200rl_logprob_entropy_fwd")
+    return logp, ent, lse, rmax, rmin
+
+
+@logprob_entropy_fwd.register_fake
+def _(logits, labels, temperature, need_entropy, need_minmax):
+    T = logits.shape[0]
+    mk = lambda n: logits.new_empty((n,), dtype=torch.float32)
+    return mk(T), mk(T if need_entropy else 0), mk(T), mk(T if need_minmax else 0), mk(T if need_minmax else 0)
+
+
+@torch.library.custom_op("b200rl::logprob_entropy_bwd", mutates_args=())
+def logprob_entropy_bwd(
+    logits: Tensor, labels: Tensor, lse: Tensor, entropy: Tensor, g_logp: Tensor,
+    g_ent: Optional[Tensor], temperature: float,
+) -> Tensor:
+    """dlogits[T, V] in the logits dtype (what autograd returns for `logits.float()`)."""
+    _check_logits(logits, labels)
+    T, V = logits.shape
+    dev = logits.device
+    g_logp = g_logp.to(torch.float32).contiguous()
+    if g_ent is not None:
+        g_ent = g_ent.to(torch.float32).contiguous()
+        if entropy.numel() != T:
+            raise RuntimeError("entropy gradient given but the forward did not compute the entropy")
+    dlogits = torch.empty((T, V), dtype=logits.dtype, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_logprob_entropy_bwd(
+            ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
+            ptr(labels), ptr(lse), ptr(entropy) if g_ent is not None else None, ptr(g_logp),
+            ptr(g_ent), T, V, float(temperature), ptr(dlogits), V, stream_handle(dev),
+        )
+    check(rc, "b200rl_logprob_entropy_bwd")
+    return dlogits
+
+
+@logprob_entropy_bwd.register_fake
+def _(logits, labels, lse, entropy, g_logp, g_ent, temperature):
+    return logits.new_empty(logits.shape)
+
+
+def _lp_setup_context(ctx, inputs, output):
+    logits, labels, temperature, need_entropy, _ = inputs
+    _, ent, lse, _, _ = output
+    ctx.save_for_backward(logits, labels, lse, ent)
+    ctx.temperature = temperature
+    ctx.need_entropy = need_entropy
+
+
+def _lp_backward(ctx, g_logp, g_ent, g_lse, g_max, g_min):
+    logits, labels, lse, ent = ctx.saved_tensors
+    if g_logp is None:
+        g_logp = torch.zeros_like(lse)
+    use_ent = ctx.need_entropy and g_ent is not None
+    dlogits = logprob_entropy_bwd(
+        logits, labels, lse, ent, g_logp, g_ent if use_ent else None, ctx.temperature
+    )
+    return dlogits, None, None, None, None
+
+
+logprob_entropy_fwd.register_autograd(_lp_backward, setup_context=_lp_setup_context)
+
+
+# --------------------------------------------------------------------------------------------
+# H3 GAE
+# --------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200rl::gae_1d_nolp_misalign", mutates_args=())
+def gae_1d_nolp_misalign(
+    rewards: Tensor, values: Tensor, cu_seqlens: Tensor, bootstrap: Tensor, gamma: float,
+    lam: float, mode: int,
+) -> Tuple[Tensor, Tensor]:
+    # checks of csrc/cugae/gae.cu:36-50, minus the two .item() host syncs on cu_seqlens
+    _lib.require_cuda(rewards=rewards, values=values, cu_seqlens=cu_seqlens, bootstrap=bootstrap)
+    _lib.require_contiguous(rewards=rewards, values=values, cu_seqlens=cu_seqlens, bootstrap=bootstrap)
+    if not (rewards.dim() == values.dim() == cu_seqlens.dim() == 1):
+        raise RuntimeError("rewards, values and cu_seqlens must be 1-D")
+    batch = cu_seqlens.numel() - 1
+    total = rewards.shape[0]
+    if bootstrap.shape != (batch,):
+        raise RuntimeError(f"bootstrap must have shape ({batch},)")
+    if values.shape != (total + batch,):
+        raise RuntimeError(f"values must have shape ({total + batch},)")
+    if bootstrap.dtype != torch.bool:
+        raise RuntimeError("bootstrap must be bool")
+    if cu_seqlens.dtype != torch.int32:
+        raise RuntimeError("cu_seqlens must be int32")
+    if rewards.dtype != torch.float32 or values.dtype != torch.float32:
+        raise RuntimeError("rewards and values must be float32")
+    dev = rewards.device
+    adv = torch.zeros_like(rewards)  # gae.cu:53-54
+    ret = torch.zeros_like(rewards)
+    if batch <= 0 or total == 0:
+        return adv, ret
+    ws_bytes = lib.b200rl_gae_workspace_bytes(batch, total)
+    ws = _lib.workspace(ws_bytes, dev)
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_gae_1d_nolp_misalign(
+            ptr(rewards), ptr(values), ptr(cu_seqlens), ptr(bootstrap), ptr(adv), ptr(ret),
+            batch, total, float(gamma), float(lam), int(mode), ptr(ws), ws.numel(),
+            stream_handle(dev),
+        )
+    check(rc, "b200rl_gae_1d_nolp_misalign")
+    return adv, ret
+
+
+@gae_1d_nolp_misalign.register_fake
+def _(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode):
+    return torch.empty_like(rewards), torch.empty_like(rewards)
+
+
+# --------------------------------------------------------------------------------------------
+# H2 PPO loss
+# --------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200rl::ppo_loss_fwd", mutates_args=())
+def ppo_loss_fwd(
+    logp: Tensor, prox_logp: Tensor, old_logp: Tensor, adv: Tensor, mask: Tensor,
+    clip_lo: float, clip_hi: float, c_clip: float, cap: float,
+    adv_mean: Optional[Tensor], adv_denom: Optional[Tensor], adv_group: Optional[Tensor],
+) -> List[Tensor]:
+    """-> [loss(0-d), denom(1), dlogp, adv_used, stat_loss, imp_w, approx_kl, clip_mask(u8),
+    dual_clip_mask(u8), behave_imp_weight, behave_approx_kl, behave_mask(u8)]"""
+    _lib.require_cuda(logp=logp, prox_logp=prox_logp, old_logp=old_logp, adv=adv, mask=mask)
+    shape = logp.shape
+    dev = logp.device
+
+    def flat(t: Tensor, name: str) -> Tensor:
+        if t.shape != shape:
+            raise RuntimeError(f"{name} has shape {tuple(t.shape)}, expected {tuple(shape)}")
+        if t.dtype != torch.float32:
+            raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+        return t.detach().contiguous().view(-1)
+
+    lp, px, ol, ad = flat(logp, "logprobs"), flat(prox_logp, "proximal_logprobs"), \
+        flat(old_logp, "old_logprobs"), flat(adv, "advantages")
+    if mask.shape != shape:
+        raise RuntimeError(f"loss_mask has shape {tuple(mask.shape)}, expected {tuple(shape)}")
+    mk = (mask if mask.dtype == torch.bool else mask != 0).contiguous().view(-1).view(torch.uint8)
+    T = lp.numel()
+    f32 = dict(dtype=torch.float32, device=dev)
+    u8 = dict(dtype=torch.uint8, device=dev)
+    loss = torch.empty((), **f32)
+    denom = torch.empty(1, **f32)
+    dlogp = torch.empty(T, **f32)
+    fused = adv_mean is not None or adv_denom is not None
+    adv_used = torch.empty(T if fused else 0, **f32)
+    s_loss, s_iw, s_kl = torch.empty(T, **f32), torch.empty(T, **f32), torch.empty(T, **f32)
+    s_clip, s_dual = torch.empty(T, **u8), torch.empty(T, **u8)
+    s_bw, s_bkl, s_bm = torch.empty(T, **f32), torch.empty(T, **f32), torch.empty(T, **u8)
+    if adv_mean is not None:
+        adv_mean = adv_mean.to(torch.float64).contiguous()
+    if adv_denom is not None:
+        adv_denom = adv_denom.to(torch.float64).contiguous()
+    if adv_group is not None:
+        adv_group = adv_group.to(torch.int32).contiguous().view(-1)
+        if adv_group.numel() != T:
+            raise RuntimeError("adv_group must have one entry per token")
+    ws = _lib.workspace(lib.b200rl_ppo_loss_workspace_bytes(T), dev)
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_ppo_loss_fwd(
+            ptr(lp), ptr(px), ptr(ol), ptr(ad), ptr(mk), T, float(clip_lo), float(clip_hi),
+            float(c_clip), float(cap), ptr(adv_mean), ptr(adv_denom), ptr(adv_group),
+            ptr(adv_used) if fused else None,
+            ptr(s_loss), ptr(s_iw), ptr(s_kl), ptr(s_clip), ptr(s_dual), ptr(s_bw), ptr(s_bkl),
+            ptr(s_bm), ptr(dlogp), ptr(loss), ptr(denom), ptr(ws), ws.numel(), stream_handle(dev),
+        )
+    check(rc, "b200rl_ppo_loss_fwd")
+    rs = lambda t: t.view(shape)
+    return [loss, denom, rs(dlogp), rs(adv_used) if fused else adv_used, rs(s_loss), rs(s_iw),
+            rs(s_kl), rs(s_clip), rs(s_dual), rs(s_bw), rs(s_bkl), rs(s_bm)]
+
+
+@ppo_loss_fwd.register_fake
+def _(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap, adv_mean, adv_denom, adv_group):
+    f = lambda: torch.empty_like(logp, dtype=torch.float32)
+    b = lambda: torch.empty_like(logp, dtype=torch.uint8)
+    fused = adv_mean is not None or adv_denom is not None
+    return [logp.new_empty((), dtype=torch.float32), logp.new_empty((1,), dtype=torch.float32), f(),
+            f() if fused else logp.new_empty((0,), dtype=torch.float32), f(), f(), f(), b(), b(),
+            f(), f(), b()]
+
+
+@torch.library.custom_op("b200rl::ppo_loss_bwd", mutates_args=())
+def ppo_loss_bwd(dlogp: Tensor, grad_loss: Tensor, denom: Tensor) -> Tensor:
+    _lib.require_cuda(dlogp=dlogp, grad_loss=grad_loss, denom=denom)
+    dev = dlogp.device
+    d = dlogp.contiguous()
+    g = torch.empty_like(d)
+    gl = grad_loss.to(torch.float32).reshape(1).contiguous()
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_ppo_loss_bwd(ptr(d), ptr(gl), ptr(denom), ptr(g), d.numel(), stream_handle(dev))
+    check(rc, "b200rl_ppo_loss_bwd")
+    return g
+
+
+@ppo_loss_bwd.register_fake
+def _(dlogp, grad_loss, denom):
+    return torch.empty_like(dlogp)
+
+
+def _loss_setup_context(ctx, inputs, output):
+    ctx.save_for_backward(output[2], output[1])
+
+
+def _loss_backward(ctx, grads):
+    dlogp, denom = ctx.saved_tensors
+    g_loss = grads[0]
+    g_lp = None
+    if g_loss is not None:
+        g_lp = ppo_loss_bwd(dlogp, g_loss, denom)
+    # like the reference in practice: only `logprobs` carries a gradient
+    return (g_lp,) + (None,) * 11
+
+
+ppo_loss_fwd.register_autograd(_loss_backward, setup_context=_loss_setup_context)
+
+
+# --------------------------------------------------------------------------------------------
+# H2 masked moments / normalisation
+# --------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200rl::masked_moments", mutates_args=())
+def masked_moments(
+    x: Tensor, mask: Optional[Tensor], group_elems: int, center: Optional[Tensor],
+    center_group_elems: int,
+) -> Tensor:
+    """x, mask: flat fp32 -> moments [G, 3] fp64 = (sum mask, sum x*mask, sum ((x-center)*mask)^2)."""
+    _lib.require_cuda(x=x, mask=mask, center=center)
+    _lib.require_contiguous(x=x, mask=mask, center=center)
+    n = x.numel()
+    dev = x.device
+    G = n // group_elems if group_elems > 0 else 0
+    mom = torch.empty((G, 3), dtype=torch.float64, device=dev)
+    if n == 0:
+        return mom
+    ws = _lib.workspace(lib.b200rl_moments_workspace_bytes(n, group_elems), dev)
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_masked_moments(
+            ptr(x), ptr(mask), n, group_elems, ptr(center), center_group_elems, ptr(mom),
+            ptr(ws), ws.numel(), stream_handle(dev),
+        )
+    check(rc, "b200rl_masked_moments")
+    return mom
+
+
+@masked_moments.register_fake
+def _(x, mask, group_elems, center, center_group_elems):
+    return x.new_empty((x.numel() // group_elems, 3), dtype=torch.float64)
+
+
+@torch.library.custom_op("b200rl::moments_finalize", mutates_args=())
+def moments_finalize(moments: Tensor, centered: bool, unbiased: bool, eps: float) -> Tuple[Tensor, Tensor]:
+    """-> (mean[G], denom[G] = sqrt(var) + eps), fp64."""
+    _lib.require_cuda(moments=moments)
+    _lib.require_contiguous(moments=moments)
+    G = moments.shape[0]
+    dev = moments.device
+    mean = torch.empty(G, dtype=torch.float64, device=dev)
+    denom = torch.empty(G, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_moments_finalize(ptr(moments), G, int(centered), int(unbiased), float(eps),
+                                         ptr(mean), ptr(denom), stream_handle(dev))
+    check(rc, "b200rl_moments_finalize")
+    return mean, denom
+
+
+@moments_finalize.register_fake
+def _(moments, centered, unbiased, eps):
+    G = moments.shape[0]
+    return moments.new_empty((G,)), moments.new_empty((G,))
+
+
+@torch.library.custom_op("b200rl::masked_normalize", mutates_args=())
+def masked_normalize(
+    x: Tensor, mask: Optional[Tensor], mean: Optional[Tensor], mean_group_elems: int,
+    denom: Optional[Tensor], denom_group_elems: int, mask_x: bool,
+) -> Tensor:
+    _lib.require_cuda(x=x, mask=mask, mean=mean, denom=denom)
+    _lib.require_contiguous(x=x, mask=mask, mean=mean, denom=denom)
+    out = torch.empty_like(x, dtype=torch.float32)
+    dev = x.device
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_masked_normalize(
+            ptr(x), ptr(mask), x.numel(), ptr(mean), mean_group_elems, ptr(denom),
+            denom_group_elems, int(mask_x), ptr(out), stream_handle(dev),
+        )
+    check(rc, "b200rl_masked_normalize")
+    return out
+
+
+@masked_normalize.register_fake
+def _(x, mask, mean, mean_group_elems, denom, denom_group_elems, mask_x):
+    return torch.empty_like(x, dtype=torch.float32)
+
+
+# --------------------------------------------------------------------------------------------
+# H4 interval gather / scatter
+# --------------------------------------------------------------------------------------------
+def _check_intervals(intervals: Tensor) -> int:
+    if not intervals.is_cuda:
+        raise RuntimeError("intervals must be on CUDA")
+    if intervals.dtype != torch.int64:
+        raise RuntimeError("intervals must be of type long")
+    if intervals.dim() != 2 or intervals.shape[1] != 2:
+        raise RuntimeError("intervals must have shape (N, 2)")
+    if not intervals.is_contiguous():
+        raise RuntimeError("intervals must be contiguous")
+    return intervals.shape[0]
+
+
+@torch.library.custom_op("b200rl::slice_intervals", mutates_args=("workspace",))
+def slice_intervals_op(
+    src: Tensor, intervals: Tensor, total_size: int, workspace: Tensor, reuse_plan: bool
+) -> Tensor:
+    _lib.require_cuda(src=src, workspace=workspace)
+    _lib.require_contiguous(src=src)
+    n = _check_intervals(intervals)
+    dev = src.device
+    dst = torch.empty((total_size,), dtype=src.dtype, device=dev)  # interval_op.cu:82
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_slice_intervals(
+            ptr(src), src.numel(), ptr(dst), total_size, ptr(intervals), n, src.element_size(),
+            ptr(workspace), workspace.numel(), int(reuse_plan), stream_handle(dev),
+        )
+    check(rc, "b200rl_slice_intervals")
+    return dst
+
+
+@slice_intervals_op.register_fake
+def _(src, intervals, total_size, workspace, reuse_plan):
+    return src.new_empty((total_size,))
+
+
+@torch.library.custom_op("b200rl::set_intervals", mutates_args=("dst", "workspace"))
+def set_intervals_op(
+    src: Tensor, dst: Tensor, intervals: Tensor, workspace: Tensor, reuse_plan: bool
+) -> None:
+    _lib.require_cuda(src=src, dst=dst, workspace=workspace)
+    _lib.require_contiguous(src=src, dst=dst)
+    if src.dtype != dst.dtype:
+        raise RuntimeError("Source and destination tensors must have the same dtype")
+    n = _check_intervals(intervals)
+    dev = src.device
+    with torch.cuda.device(dev):
+        rc = lib.b200rl_set_intervals(
+            ptr(src), src.numel(), ptr(dst), dst.numel(), ptr(intervals), n, src.element_size(),
+            ptr(workspace), workspace.numel(), int(reuse_plan), stream_handle(dev),
+        )
+    check(rc, "b200rl_set_intervals")

@@ -1,0 +1,149 @@
+"""Drop-in for the GAE entry points and the legacy actor loss of
+``realhf/impl/model/utils/ppo_functional.py`` and for the ``cugae`` / ``realhf._C.cugae`` binding.
+
+Reference: ppo_functional.py:51-149 (actor_loss_fn), :292-323 (pygae1d_nolp_misalign),
+:326-366 (cugae1d_nolp_misalign_func), :369-394 (get_packed_advantages_and_returns);
+csrc/cugae/gae.cu:30-60 (gae_1d_nolp_misalign).
+"""
+
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import _lib, ops
+
+__all__ = [
+    "gae_1d_nolp_misalign",
+    "cugae1d_nolp_misalign_func",
+    "pygae1d_nolp_misalign",
+    "get_packed_advantages_and_returns",
+    "actor_loss_fn",
+]
+
+_MODES = {"auto": _lib.GAE_AUTO, "serial": _lib.GAE_SERIAL, "scan": _lib.GAE_SCAN}
+
+
+def gae_1d_nolp_misalign(
+    rewards: torch.Tensor,
+    values: torch.Tensor,
+    cu_seqlens: torch.Tensor,
+    bootstrap: torch.Tensor,
+    gamma: float,
+    lmbda: float,
+    mode: str = "auto",
+) -> List[torch.Tensor]:
+    """The pybind entry ``realhf._C.cugae.gae_1d_nolp_misalign`` (gae.cu:30-60): same argument
+    checks (device, contiguity, shapes, dtypes) raising RuntimeError, returns ``[adv, ret]``.
+    The reference's two ``.item()`` checks on cu_seqlens (gae.cu:48-49) are host syncs and are
+    not repeated here. ``mode``: "auto" | "serial" | "scan" (see include/b200rl.h)."""
+    adv, ret = ops.gae_1d_nolp_misalign(
+        rewards, values, cu_seqlens, bootstrap, float(gamma), float(lmbda), _MODES[mode]
+    )
+    return [adv, ret]
+
+
+def cugae1d_nolp_misalign_func(
+    rewards: torch.Tensor,
+    values: torch.Tensor,
+    cu_seqlens: torch.Tensor,
+    truncate: torch.Tensor,
+    gamma: float,
+    lam: float,
+) -> Tuple[torch.Tensor, torch.Tensor]:
+    """GAE over packed sequences; ``values`` is longer than ``rewards`` by one bootstrap slot
+    per sequence, ``truncate[i]`` says whether sequence i's last next-value is bootstrapped
+    (ref ppo_functional.py:326-366). The reference's two asserts on ``cu_seqlens[0]`` /
+    ``cu_seqlens[-1]`` force device->host syncs (:365); they are dropped."""
+    assert len(rewards.shape) == len(values.shape) == len(cu_seqlens.shape) == 1
+    adv, ret = gae_1d_nolp_misalign(rewards, values, cu_seqlens, truncate, gamma, lam)
+    return adv, ret
+
+
+def pygae1d_nolp_misalign(
+    rewards: torch.Tensor,
+    values: torch.Tensor,
+    cu_seqlens_: torch.Tensor,
+    bootstrap: torch.Tensor,
+    gamma: float,
+    lam: float,
+) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Same contract as the reference's python loop (ppo_functional.py:292-323), computed by the
+    CUDA kernel in its reference-order (serial) mode. Unlike the reference it does not zero
+    ``values`` in place when ``bootstrap[i] == 0`` (:313-315 mutates through a view)."""
+    if not rewards.is_cuda:
+        raise RuntimeError(
+            "pygae1d_nolp_misalign: CPU tensors are not supported (b200rl has no CPU path; "
+            "the CPU oracle lives under oracle/ and is test infrastructure)"
+        )
+    adv, ret = gae_1d_nolp_misalign(
+        rewards.float(), values.float(), cu_seqlens_.int(), bootstrap.bool(), gamma, lam, mode="serial"
+    )
+    return adv, ret
+
+
+@torch.no_grad()
+def get_packed_advantages_and_returns(
+    gamma: float,
+    lam: float,
+    values: torch.Tensor,
+    rewards: torch.Tensor,
+    short1cu_seqlens: torch.Tensor,
+    seq_no_eos_mask: torch.Tensor,
+) -> Tuple[torch.Tensor, torch.Tensor]:
+    """ref ppo_functional.py:369-394. The reference silently falls back to the python loop on
+    CPU tensors or when the extension is missing; here CUDA is the only path."""
+    return cugae1d_nolp_misalign_func(
+        rewards, values, short1cu_seqlens.int(), seq_no_eos_mask.bool(), gamma, lam
+    )
+
+
+def actor_loss_fn(
+    logprobs: torch.Tensor,
+    old_logprobs: torch.Tensor,
+    advantages: torch.Tensor,
+    eps_clip: float,
+    loss_mask: Optional[torch.Tensor] = None,
+    c_clip: Optional[float] = None,
+    proximal_logprobs: Optional[torch.Tensor] = None,
+    behav_imp_weight_cap: Optional[float] = None,
+) -> Tuple[torch.Tensor, Dict]:
+    """Legacy twin of ppo_actor_loss_fn (ref ppo_functional.py:51-149): no ``eps_clip_higher``;
+    ``loss_mask`` optional (all ones); without ``proximal_logprobs`` the ratio is taken against
+    ``old_logprobs`` and there is no behaviour weight (and no behave_* stats)."""
+    assert logprobs.dtype == torch.float32
+    assert old_logprobs.dtype == torch.float32
+    assert advantages.dtype == torch.float32
+    if c_clip is not None:
+        assert c_clip > 1.0, c_clip
+    if loss_mask is None:
+        loss_mask = torch.ones_like(logprobs, dtype=torch.bool)
+    denorm = proximal_logprobs if proximal_logprobs is not None else old_logprobs
+    out = ops.ppo_loss_fwd(
+        logprobs,
+        denorm,
+        old_logprobs if proximal_logprobs is not None else denorm,  # prox == old -> weight 1
+        advantages,
+        loss_mask,
+        1.0 - eps_clip,
+        1.0 + eps_clip,
+        -1.0 if c_clip is None else float(c_clip),
+        -2.0 if proximal_logprobs is None
+        else (-1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap)),
+        None,
+        None,
+        None,
+    )
+    stat = dict(
+        loss=out[4],
+        importance_weight=out[5],
+        approx_kl=out[6],
+        clip_mask=out[7].view(torch.bool),
+        dual_clip_mask=out[8].view(torch.bool),
+    )
+    if proximal_logprobs is not None:
+        stat["behave_imp_weight"] = out[9]
+        stat["behave_approx_kl"] = out[10]
+        stat["behave_mask"] = out[11].view(torch.bool)
+    return out[0], stat

@@ -1,0 +1,186 @@
+/* b200rl — C ABI of the B200-native per-token RL math library (libb200rl.so).
+ *
+ * Every entry point is `extern "C"`, takes plain device/host pointers, sizes and a
+ * CUDA stream handle (`void*`, a cudaStream_t; NULL = legacy default stream), and
+ * returns an int: 0 on success, a positive cudaError_t value if a CUDA call failed,
+ * a negative B200RL_E* code for argument errors. `b200rl_last_error()` returns a
+ * thread-local, human readable description of the last non-zero return.
+ *
+ * The library never allocates device memory: the caller owns every buffer,
+ * including the scratch ("workspace") buffers whose size the *_workspace_bytes
+ * helpers report. Nothing here synchronises the host with the device.
+ *
+ * Citations `ref:` are relative to the AReaL-vllm reference tree and name the
+ * reference interface that each entry point replaces.
+ */
+#ifndef B200RL_H_
+#define B200RL_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200RL_OK 0
+#define B200RL_EINVAL (-1)       /* bad argument (null pointer, negative size, misalignment) */
+#define B200RL_EUNSUPPORTED (-2) /* dtype / mode not built */
+#define B200RL_EWORKSPACE (-3)   /* workspace too small */
+
+/* element types of a logits / parameter buffer */
+#define B200RL_BF16 0
+#define B200RL_FP16 1
+#define B200RL_FP32 2
+
+const char* b200rl_last_error(void);
+int b200rl_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * H1  log-prob / entropy gather over [T, V] logits.
+ * ref: areal/utils/functional.py:10-16 (_gather_logprobs), :19-26 (_gather_logprobs_entropy),
+ *      :29-80 (chunking wrappers; chunking is unnecessary here, results do not depend on it).
+ *
+ * fwd:  x = logits/temperature (fp32);  lse[t] = logsumexp_j x[t,j];
+ *       logp[t] = x[t,labels[t]] - lse[t];  entropy[t] = -sum_j p_j log p_j.
+ *       One streaming pass over the row (online softmax). `entropy`, `rowmax`, `rowmin` may be
+ *       NULL. `rowmax/rowmin` are the raw (un-tempered) per-row logits extrema that
+ *       grpo_loss_fn logs (ref: areal/engine/ppo/actor.py:351-352).
+ * bwd:  dlogits[t,j] = (1/temperature) * ( g_logp[t]*(1[j==y_t] - p_j) - g_ent[t]*p_j*(log p_j + H_t) )
+ *       rounded to the logits dtype; the softmax is recomputed from `lse`, never stored.
+ *       `g_ent` may be NULL (entropy detached, the GRPO call site); then `entropy` may be NULL too.
+ * `ld` / `ld_out` are row strides in elements. `dtype` is B200RL_BF16 / FP16 / FP32.
+ */
+int b200rl_logprob_entropy_fwd(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                               int64_t T, int64_t V, float temperature, float* logp,
+                               float* entropy, float* lse, float* rowmax, float* rowmin,
+                               void* stream);
+
+int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                               const float* lse, const float* entropy, const float* g_logp,
+                               const float* g_ent, int64_t T, int64_t V, float temperature,
+                               void* dlogits, int64_t ld_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * H3  GAE over packed variable-length sequences ("1d, no-overlap, misaligned").
+ * ref: csrc/cugae/gae.cu:10-60 (gae_kernel_1d_nolp_misalign + launcher),
+ *      realhf/impl/model/utils/ppo_functional.py:292-366 (pygae1d_nolp_misalign, cugae1d_nolp_misalign_func).
+ *
+ * rewards/adv/ret: [total] fp32; values: [total + batch] fp32 (sequence i's values start at
+ * cu_seqlens[i] + i); cu_seqlens: [batch+1] int32; bootstrap: [batch] bytes (0/1).
+ *   delta_t = r_t + gamma * v_{t+1} * (t is last ? bootstrap : 1) - v_t
+ *   adv_t   = delta_t + gamma*lam * adv_{t+1};   ret_t = adv_t + v_t.
+ * mode: B200RL_GAE_AUTO picks SERIAL when gamma*lam is so close to 1 that re-associating the
+ * fp32 additions would move results by more than the 1e-5 parity bar, else SCAN.
+ *   SERIAL — one warp per sequence; the recurrence is evaluated in the reference's order
+ *            (bit-identical to the reference CUDA kernel), loads/stores are warp-coalesced.
+ *   SCAN   — segmented reverse affine scan over fixed tiles of the packed stream with a
+ *            decoupled look-back across tiles (long sequences spread over many warps).
+ * SCAN needs `workspace` of b200rl_gae_workspace_bytes(); it is cleared by the call itself.
+ */
+#define B200RL_GAE_AUTO 0
+#define B200RL_GAE_SERIAL 1
+#define B200RL_GAE_SCAN 2
+size_t b200rl_gae_workspace_bytes(int32_t batch, int64_t total);
+int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
+                                const int32_t* cu_seqlens, const uint8_t* bootstrap, float* adv,
+                                float* ret, int32_t batch, int64_t total, float gamma, float lam,
+                                int mode, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * H2  clipped PPO / GRPO actor loss with decoupled-PPO behaviour weights.
+ * ref: areal/utils/functional.py:124-188 (ppo_actor_loss_fn);
+ *      twin realhf/impl/model/utils/ppo_functional.py:51-149 (actor_loss_fn).
+ *
+ * All per-token arrays have T elements. `mask` is bytes (bool). `clip_lo`/`clip_hi` are the
+ * clamp bounds 1-eps_clip and 1+(eps_clip_higher or eps_clip), computed by the caller in double
+ * and rounded to fp32 exactly as torch.clamp receives them (functional.py:146-150).
+ * `c_clip` <= 0 means None, `cap` < 0 means None; `cap` == -2 switches the behaviour weight off
+ * altogether (w = 1 on every token: the legacy actor_loss_fn called without proximal_logprobs).
+ * Optional fused advantage normalisation (north_star kernel 3): when `adv_mean` or `adv_denom`
+ * is non-NULL the kernel uses
+ *     A_t = float( ((double)adv[t]*mask_f[t] - adv_mean[g]) / adv_denom[g] ),  g = adv_group[t]
+ * (g = 0 when adv_group is NULL; a NULL mean is 0, a NULL denom is 1) — the arithmetic of
+ * masked_normalization (ref: areal/utils/functional.py:83-121) — and, when `adv_out` is
+ * non-NULL, also writes the normalised advantage there.
+ * Outputs: the eight stat arrays of the reference (`stat_*`, any may be NULL), `loss[0]` (fp32
+ * scalar = sum(mask*pg)/N), `denom[0]` (fp32, N = max(count(mask),1)), and, if non-NULL,
+ * `dlogp[t]` = d(N*loss)/d logp[t] (NOT yet divided by N) for the backward.
+ * `workspace`: b200rl_ppo_loss_workspace_bytes(T) bytes; cleared by the call itself.
+ * The reduction order is fixed (deterministic loss bits for a given T).
+ */
+size_t b200rl_ppo_loss_workspace_bytes(int64_t T);
+int b200rl_ppo_loss_fwd(const float* logp, const float* prox_logp, const float* old_logp,
+                        const float* adv, const uint8_t* mask, int64_t T, float clip_lo,
+                        float clip_hi, float c_clip, float cap, const double* adv_mean,
+                        const double* adv_denom, const int32_t* adv_group, float* adv_out,
+                        float* stat_loss, float* stat_imp_weight, float* stat_approx_kl,
+                        uint8_t* stat_clip_mask, uint8_t* stat_dual_clip_mask,
+                        float* stat_behave_imp_weight, float* stat_behave_approx_kl,
+                        uint8_t* stat_behave_mask, float* dlogp, float* loss, float* denom,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* backward of the scalar loss: g_logp[t] = grad_loss[0] * dlogp[t] / denom[0]; grad_loss and
+ * denom are DEVICE scalars, so there is no host sync (the reference syncs at
+ * `count_nonzero() or 1`, functional.py:143). ref: autograd of functional.py:143-175. */
+int b200rl_ppo_loss_bwd(const float* dlogp, const float* grad_loss, const float* denom,
+                        float* g_logp, int64_t T, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * H2  masked moments + normalisation (advantage normalisation, batch / group level).
+ * ref: areal/utils/functional.py:83-121 (masked_normalization),
+ *      areal/engine/ppo/actor.py:412-604 (AdvNorm.__call__, _compute_mean, _compute_std).
+ *
+ * x: [n_elems] fp32; moment group g owns the contiguous slice [g*group_elems, (g+1)*group_elems)
+ * (n_elems must be a multiple of group_elems). mask: same shape, fp32 weights, or NULL (ones).
+ *   moments[g] = { sum(mask), sum(x*mask), sum(((x - center[i / center_group_elems])*mask)^2) }
+ * in fp64 (center == NULL -> 0: the raw second moment). Fixed summation order.
+ * `workspace`: b200rl_moments_workspace_bytes(n_elems, group_elems); cleared by the call.
+ * finalize: mean = m1/m0; var = centered ? m2/m0 : m2/m0 - mean^2; unbiased: var *= m0/(m0-1);
+ *           denom = sqrt(var) + eps.   (functional.py:116-121, actor.py:600-604)
+ * normalize: out[i] = float( ((double)x[i]*(mask_x ? mask[i] : 1) - mean[i/mean_group_elems])
+ *                            / denom[i/denom_group_elems] );  NULL mean = 0, NULL denom = 1.
+ */
+size_t b200rl_moments_workspace_bytes(int64_t n_elems, int64_t group_elems);
+int b200rl_masked_moments(const float* x, const float* mask, int64_t n_elems,
+                          int64_t group_elems, const double* center, int64_t center_group_elems,
+                          double* moments, void* workspace, size_t workspace_bytes, void* stream);
+int b200rl_moments_finalize(const double* moments, int64_t n_groups, int centered, int unbiased,
+                            double eps, double* mean, double* denom, void* stream);
+int b200rl_masked_normalize(const float* x, const float* mask, int64_t n_elems,
+                            const double* mean, int64_t mean_group_elems, const double* denom,
+                            int64_t denom_group_elems, int mask_x, float* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * H4  interval gather / scatter on a flat parameter buffer.
+ * ref: csrc/interval_op/interval_op.cu:12-114 (copyDataKernel, slice_intervals, set_intervals),
+ *      realhf/impl/model/nn/flatten_param.py:65-186 (python wrappers and fallbacks),
+ *      csrc/interval_op/interval_op.cpp:4-25 (merge_intervals).
+ *
+ * intervals: DEVICE int64 [n, 2] of [start, end) element offsets into the big buffer.
+ * slice: packed[off_i : off_i + len_i] = big[start_i : end_i]    (off = exclusive prefix sum of len)
+ * set:   big[start_i : end_i] = packed[off_i : off_i + len_i]
+ * Pure byte moves, bit-exact for any payload. elem_size in {1,2,4,8}.
+ * `packed_numel` is the packed side's element count (slice: output size; set: src size).
+ * workspace: b200rl_interval_workspace_bytes(n, packed_numel, elem_size) bytes. The plan
+ * (prefix sums + tile->interval map) is rebuilt on every call unless `reuse_plan` != 0, in which
+ * case the workspace must hold the plan of a previous call with identical intervals.
+ * After the call workspace's first int64 holds the sum of interval lengths and the second a
+ * non-zero flag if an interval was malformed or out of bounds (nothing is copied for those).
+ */
+size_t b200rl_interval_workspace_bytes(int64_t n_intervals, int64_t packed_numel, int elem_size);
+int b200rl_slice_intervals(const void* big, int64_t big_numel, void* packed, int64_t packed_numel,
+                           const int64_t* intervals, int64_t n_intervals, int elem_size,
+                           void* workspace, size_t workspace_bytes, int reuse_plan, void* stream);
+int b200rl_set_intervals(const void* packed, int64_t packed_numel, void* big, int64_t big_numel,
+                         const int64_t* intervals, int64_t n_intervals, int elem_size,
+                         void* workspace, size_t workspace_bytes, int reuse_plan, void* stream);
+
+/* host: merge touching neighbours [a,b),[b,c) -> [a,c), order preserving, no sort.
+ * in/out: n (resp. return value) pairs of uint64. out may alias in. */
+size_t b200rl_merge_intervals(const uint64_t* in, size_t n, uint64_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RL_H_ */

@@ -1,0 +1,110 @@
+"""Loads the REAL reference functions from /root/reference (build container only).
+TEST INFRASTRUCTURE: used by gen_golden.py to produce tests/golden/*, and by
+tests/test_reference_live.py when the tree is present. Nothing under -m gpu, smoke() or
+bench.py touches this module (/root/reference does not exist on the GPU box).
+
+No reference source is copied: modules are imported from where they lie, with stub modules for
+the dependencies that are absent here (tensordict, omegaconf-based realhf.base).
+"""
+
+from __future__ import annotations
+
+import ast
+import importlib.util
+import os
+import sys
+import types
+
+REF_ROOT = os.environ.get("B200RL_REFERENCE", "/root/reference")
+
+
+def available() -> bool:
+    return os.path.isdir(os.path.join(REF_ROOT, "areal"))
+
+
+def areal_functional():
+    """areal/utils/functional.py with `tensordict` stubbed and torch.compile bypassed
+    (Inductor's CPU backend cannot build in this container; the eager originals are the
+    'reference fp32 torch path')."""
+    os.environ.setdefault("TORCHDYNAMO_DISABLE", "1")
+    if "tensordict" not in sys.modules:
+        td = types.ModuleType("tensordict")
+        td.TensorDict = dict
+        sys.modules["tensordict"] = td
+    path = os.path.join(REF_ROOT, "areal/utils/functional.py")
+    spec = importlib.util.spec_from_file_location("_ref_areal_functional", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    for name in ("_gather_logprobs", "_gather_logprobs_entropy"):
+        fn = getattr(mod, name)
+        orig = getattr(fn, "_torchdynamo_orig_callable", None)
+        if orig is not None:
+            setattr(mod, name, orig)
+    return mod
+
+
+def realhf_ppo_functional():
+    """realhf/impl/model/utils/ppo_functional.py loaded by path with stub `realhf.base`."""
+    for name in ("realhf", "realhf.base", "realhf.base.pkg_version"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    sys.modules["realhf.base.pkg_version"].is_available = lambda n: False
+    sys.modules["realhf.base"].pkg_version = sys.modules["realhf.base.pkg_version"]
+    sys.modules["realhf"].base = sys.modules["realhf.base"]
+    path = os.path.join(REF_ROOT, "realhf/impl/model/utils/ppo_functional.py")
+    spec = importlib.util.spec_from_file_location("_ref_ppo_functional", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _extract(path: str, names, extra_globals=None):
+    """exec only the named top-level functions/classes of a reference file."""
+    src = open(path).read()
+    tree = ast.parse(src)
+    keep = [n for n in tree.body
+            if isinstance(n, (ast.FunctionDef, ast.ClassDef)) and n.name in names]
+    g = dict(extra_globals or {})
+    exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), g)
+    return g
+
+
+def flatten_param_py():
+    """_slice_intervals_py / _set_intervals_py (realhf/impl/model/nn/flatten_param.py:65-90)."""
+    import torch
+    from typing import List, Tuple
+
+    return _extract(
+        os.path.join(REF_ROOT, "realhf/impl/model/nn/flatten_param.py"),
+        {"_slice_intervals_py", "_set_intervals_py"},
+        dict(torch=torch, List=List, Tuple=Tuple),
+    )
+
+
+def adv_norm_class():
+    """AdvNorm (areal/engine/ppo/actor.py:370-604) bound to the real masked_normalization."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from typing import Optional
+
+    F = areal_functional()
+    g = _extract(
+        os.path.join(REF_ROOT, "areal/engine/ppo/actor.py"),
+        {"AdvNorm"},
+        dict(torch=torch, np=np, dist=dist, Optional=Optional,
+             masked_normalization=F.masked_normalization),
+    )
+    return g["AdvNorm"]
+
+
+def merge_intervals_ext():
+    """The reference's own merge_intervals, compiled by oracle/Makefile into oracle/_ref/."""
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+    for f in os.listdir(here) if os.path.isdir(here) else []:
+        if f.startswith("interval_op") and f.endswith(".so"):
+            spec = importlib.util.spec_from_file_location("interval_op", os.path.join(here, f))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            return mod.merge_intervals
+    return None

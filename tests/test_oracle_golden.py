@@ -1,0 +1,135 @@
+"""The CPU oracle against the fixtures that oracle/gen_golden.py produced from the REAL reference
+(areal/utils/functional.py, areal/engine/ppo/actor.py, realhf/.../ppo_functional.py,
+realhf/.../flatten_param.py, csrc/interval_op/interval_op.cpp). This pins the oracle."""
+
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, from_bits, golden_logits, load_golden
+from oracle import cpu_ref, torch_ref
+
+H1 = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "h1_*.npz")))
+GAE = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "gae_*.npz")))
+
+
+@pytest.mark.parametrize("name", H1)
+def test_h1_forward_and_grad(name):
+    g = load_golden(name)
+    logits, dref = golden_logits(g)
+    labels = torch.from_numpy(g["labels"])
+    temp = float(g["temperature"])
+    x = logits.clone().requires_grad_(True)
+    lp, ent = torch_ref.logprobs_entropy(x, labels, temp)
+    # same torch ops as the reference: identical up to libm/threading differences between hosts
+    np.testing.assert_allclose(lp.detach().numpy(), g["logp"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(ent.detach().numpy(), g["entropy"], rtol=1e-6, atol=1e-6)
+    (lp * torch.from_numpy(g["g_logp"])).sum().add((ent * torch.from_numpy(g["g_ent"])).sum()).backward()
+    tol = 1e-6 if logits.dtype == torch.float32 else 8e-3  # one ulp of the 16-bit grad dtype
+    np.testing.assert_allclose(x.grad.float().numpy(), dref.float().numpy(), rtol=tol, atol=1e-7)
+    # fp64 ground truth agrees with the fp32 reference at the parity tolerance
+    lp64, ent64 = torch_ref.logprobs_entropy_f64(logits, labels, temp)
+    np.testing.assert_allclose(lp64.numpy(), g["logp"], rtol=1e-3, atol=1e-5)
+    np.testing.assert_allclose(ent64.numpy(), g["entropy"], rtol=1e-3, atol=1e-5)
+
+
+def _kw(g, key):
+    v = float(g["kw_" + key])
+    return None if np.isnan(v) else v
+
+
+@pytest.mark.parametrize("k", range(5))
+def test_h2_loss(k):
+    g = load_golden(f"h2_loss_{k}")
+    lp = torch.from_numpy(g["logp"]).requires_grad_(True)
+    loss, stat = torch_ref.ppo_actor_loss(
+        lp, torch.from_numpy(g["prox"]), torch.from_numpy(g["old"]), torch.from_numpy(g["adv"]),
+        _kw(g, "eps_clip"), torch.from_numpy(g["mask"]), _kw(g, "eps_clip_higher"),
+        _kw(g, "c_clip"), _kw(g, "behav_imp_weight_cap"),
+    )
+    loss.backward()
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(lp.grad.numpy(), g["g_logp"], rtol=1e-6, atol=1e-9)
+    for key, v in stat.items():
+        ref = g["stat_" + key]
+        if ref.dtype == np.bool_:
+            assert v.dtype == torch.bool and np.array_equal(v.numpy(), ref), key
+        else:
+            assert v.dtype == torch.float32
+            np.testing.assert_allclose(v.numpy(), ref, rtol=1e-6, atol=1e-7, err_msg=key)
+
+
+def test_h2_advnorm_all_levels():
+    g = load_golden("h2_advnorm")
+    for tag in ("a", "b"):
+        x, mask = torch.from_numpy(g[f"x_{tag}"]), torch.from_numpy(g[f"mask_{tag}"])
+        for m in ("batch", "group", "none"):
+            for s in ("batch", "group", "none"):
+                for use_mask in (1, 0):
+                    for unbiased in (0, 1):
+                        ref = g[f"out_{tag}_{m}_{s}_{use_mask}_{unbiased}"]
+                        out = torch_ref.adv_norm(x, mask if use_mask else None, m, s, 4,
+                                                 unbiased=bool(unbiased))
+                        assert out.shape == ref.shape and out.dtype == torch.float32
+                        np.testing.assert_allclose(out.numpy(), ref, rtol=1e-6, atol=1e-6,
+                                                   err_msg=f"{tag} {m} {s} {use_mask} {unbiased}")
+    x, mask = torch.from_numpy(g["mn_x"]), torch.from_numpy(g["mn_mask"])
+    np.testing.assert_allclose(torch_ref.masked_normalization(x, mask).numpy(), g["mn_all"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(torch_ref.masked_normalization(x).numpy(), g["mn_nomask"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(torch_ref.masked_normalization(x, mask, dim=(1,)).numpy(), g["mn_dim1"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(torch_ref.masked_normalization(x, mask, dim=(0,), unbiased=True).numpy(),
+                               g["mn_dim0_unbiased"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(torch_ref.masked_normalization(x, mask, high_precision=False).numpy(),
+                               g["mn_lowprec"], rtol=1e-5, atol=1e-5)
+    # zero input -> zero output (reference test areal/tests/test_adv_norm_config.py:243-254)
+    assert np.array_equal(g["mn_zero"], np.zeros((4, 5), np.float32))
+    assert torch.equal(torch_ref.masked_normalization(torch.zeros(4, 5), torch.ones(4, 5)), torch.zeros(4, 5))
+
+
+@pytest.mark.parametrize("name", GAE)
+def test_gae_bit_exact_vs_pygae(name):
+    g = load_golden(name)
+    adv, ret = cpu_ref.gae_py(g["rewards"], g["values"], g["cu_seqlens"], g["bootstrap"],
+                              float(g["gamma"]), float(g["lam"]))
+    assert np.array_equal(adv, g["adv"]), np.abs(adv - g["adv"]).max()
+    assert np.array_equal(ret, g["ret"])
+    # the CUDA reference's contraction (FMA) stays within the reference test's tolerance
+    # (realhf/tests/cpp_extensions/test_cugae.py:50-51, atol=1e-5 + rtol=1e-5)
+    adv_c, ret_c = cpu_ref.gae_cuda_order(g["rewards"], g["values"], g["cu_seqlens"],
+                                          g["bootstrap"], float(g["gamma"]), float(g["lam"]))
+    if float(g["gamma"]) == 1.0 and float(g["lam"]) == 1.0:
+        assert np.array_equal(adv_c, g["adv"]) and np.array_equal(ret_c, g["ret"])
+    else:
+        np.testing.assert_allclose(adv_c, g["adv"], rtol=1e-5, atol=1e-5)
+        np.testing.assert_allclose(ret_c, g["ret"], rtol=1e-5, atol=1e-5)
+
+
+def test_gae_python_loop_agrees_with_c():
+    g = load_golden("gae_small_0905")
+    a1, r1 = cpu_ref.gae_py_loops(g["rewards"], g["values"], g["cu_seqlens"], g["bootstrap"],
+                                  float(g["gamma"]), float(g["lam"]))
+    assert np.array_equal(a1, g["adv"]) and np.array_equal(r1, g["ret"])
+
+
+@pytest.mark.parametrize("tag,dtype", [("bf16_a", np.uint16), ("fp32_b", np.uint32),
+                                       ("fp16_c", np.uint16), ("adv", np.uint16)])
+def test_intervals_bit_exact(tag, dtype):
+    g = load_golden("h4_intervals")
+    iv = g[f"{tag}_intervals"]
+    src = g[f"{tag}_src_bits"].view(dtype)
+    got = cpu_ref.slice_intervals(src, iv)
+    assert np.array_equal(got, g[f"{tag}_slice_bits"].view(dtype))
+    dst = np.zeros_like(src)
+    cpu_ref.set_intervals(got, dst, iv)
+    assert np.array_equal(dst, g[f"{tag}_set_bits"].view(dtype))
+
+
+def test_merge_intervals_vs_reference_cpp():
+    g = load_golden("h4_intervals")
+    for a, b in (("merge_in", "merge_out"), ("merge_in2", "merge_out2")):
+        got = cpu_ref.merge_intervals([tuple(x) for x in g[a].tolist()])
+        assert got == [tuple(x) for x in g[b].tolist()]
+    assert cpu_ref.merge_intervals([]) == []
