@@ -196,12 +196,13 @@ def ppo_actor_loss_fn_fused_advnorm(
         -1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap),
         adv_mean, adv_denom, adv_group,
     )
+    det = [t.detach() for t in out]
     stat = dict(
-        loss=out[4], importance_weight=out[5], approx_kl=out[6],
-        clip_mask=out[7].view(torch.bool), dual_clip_mask=out[8].view(torch.bool),
-        behave_imp_weight=out[9], behave_approx_kl=out[10], behave_mask=out[11].view(torch.bool),
+        loss=det[4], importance_weight=det[5], approx_kl=det[6],
+        clip_mask=det[7].view(torch.bool), dual_clip_mask=det[8].view(torch.bool),
+        behave_imp_weight=det[9], behave_approx_kl=det[10], behave_mask=det[11].view(torch.bool),
     )
-    return out[0], stat, out[3]
+    return out[0], stat, det[3]
 
 
 @torch.no_grad()

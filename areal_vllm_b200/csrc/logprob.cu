@@ -248,7 +248,9 @@ logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
         const float l2s = log2f(S);
         const float lse2 = M + l2s;  // log2 domain
         lse[row] = lse2 * kLn2;
-        logp[row] = fmaf(xy, scale, -lse2) * kLn2;
+        // (x_y*scale - M) first: exact cancellation when the label is the row maximum, however
+        // large |M| is; only then the (small) log2 of the sum
+        logp[row] = (fmaf(xy, scale, -M) - l2s) * kLn2;
         if (ENT) ent[row] = kLn2 * (l2s - Tt / S);
         if (MINMAX) {
           if (rowmax) rowmax[row] = mx;
@@ -476,7 +478,7 @@ logprob_fwd_plain_kernel(const T* __restrict__ logits, int64_t ld, const int64_t
     const int64_t lab = labels[row];
     const float xy = (lab >= 0 && lab < V) ? to_f<T>(x[lab]) : __int_as_float(0x7fc00000);
     lse[row] = lse2 * kLn2;
-    logp[row] = fmaf(xy, scale, -lse2) * kLn2;
+    logp[row] = (fmaf(xy, scale, -m2) - l2s) * kLn2;
     if (ent) ent[row] = kLn2 * (l2s - t / s);
     if (rowmax) rowmax[row] = mx;
     if (rowmin) rowmin[row] = mn;

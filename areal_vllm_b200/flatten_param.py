@@ -66,6 +66,7 @@ def _to_cuda_intervals(intervals_cpu, device) -> torch.Tensor:
 
 
 def _slice_impl(src: torch.Tensor, intervals: torch.Tensor, total_size: int) -> torch.Tensor:
+    ops._check_intervals(intervals)
     if intervals.shape[0] == 0 or total_size == 0:
         return torch.empty((total_size,), dtype=src.dtype, device=src.device)
     ws, reuse = _plan(intervals, total_size, src.element_size(), src.numel())
@@ -73,6 +74,9 @@ def _slice_impl(src: torch.Tensor, intervals: torch.Tensor, total_size: int) -> 
 
 
 def _set_impl(src: torch.Tensor, dst: torch.Tensor, intervals: torch.Tensor) -> None:
+    ops._check_intervals(intervals)
+    if src.dtype != dst.dtype:
+        raise RuntimeError("Source and destination tensors must have the same dtype")
     if intervals.shape[0] == 0 or src.numel() == 0:
         return None
     ws, reuse = _plan(intervals, src.numel(), src.element_size(), dst.numel())

@@ -175,17 +175,18 @@ def ppo_actor_loss_fn(
         None,
     )
     loss = out[0]
+    det = [t.detach() for t in out]  # the reference's stats are detached / non-differentiable
     stat = dict(
-        loss=out[4],
-        importance_weight=out[5],
-        approx_kl=out[6],
-        clip_mask=out[7].view(torch.bool),
-        dual_clip_mask=out[8].view(torch.bool),
+        loss=det[4],
+        importance_weight=det[5],
+        approx_kl=det[6],
+        clip_mask=det[7].view(torch.bool),
+        dual_clip_mask=det[8].view(torch.bool),
     )
     if proximal_logprobs is not None:
-        stat["behave_imp_weight"] = out[9]
-        stat["behave_approx_kl"] = out[10]
-        stat["behave_mask"] = out[11].view(torch.bool)
+        stat["behave_imp_weight"] = det[9]
+        stat["behave_approx_kl"] = det[10]
+        stat["behave_mask"] = det[11].view(torch.bool)
     return loss, stat
 
 
