@@ -270,6 +270,9 @@ def grpo_loss_fn(
         proximal_logprobs=prox_logp,
         behav_imp_weight_cap=behav_imp_weight_cap,
     )
+    st = _stats_tracker()
+    if stats is None and st is None:
+        return loss  # nobody consumes the logging tensors: do not launch the derived ones
     clip_mask = stat["clip_mask"]
     new_logp = logprobs.detach()
     collected = dict(
@@ -294,7 +297,6 @@ def grpo_loss_fn(
     )
     if stats is not None:
         stats.update(collected)
-    st = _stats_tracker()
     if st is not None:
         st.denominator(
             n_tokens=torch.ones(logits.shape[0], dtype=torch.bool, device=logits.device),

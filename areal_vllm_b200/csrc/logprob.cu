@@ -32,81 +32,176 @@ constexpr uint32_t kNeutral = 0xF14AF14Au;  // bf16 pair ~ -1e30: exp -> 0, fini
 constexpr uint32_t kNegInf2 = 0xFF80FF80u;
 constexpr uint32_t kPosInf2 = 0x7F807F80u;
 
-constexpr int kChunkVec = 256;            // 16-B vectors per TMA chunk
+constexpr int kChunkVec = 256;            // 16-B vectors per full TMA chunk (8 warp-rows of 32)
 constexpr int kChunkBytes = kChunkVec * 16;
+constexpr int kSlots = 4;                 // row-result slots in flight per CTA (forward)
 
 template <int WARPS, int STAGES>
 struct FwdSmem {
   static constexpr int kData = WARPS * STAGES * kChunkBytes;
   static constexpr int kBarOff = kData;
   static constexpr int kPartOff = kBarOff + WARPS * STAGES * 8;
-  static constexpr int kBytes = kPartOff + 2 * 5 * WARPS * 4;
+  static constexpr int kCntOff = kPartOff + kSlots * 6 * WARPS * 4;  // [slot][M,S,T,mx,mn,xy][warp]
+  static constexpr int kBytes = kCntOff + 2 * kSlots * 4;            // cnt[kSlots], gen[kSlots]
 };
 
-// Producer state of one warp: walks (row iteration, chunk) pairs of the warp's slice.
-struct Producer {
-  int it, ck;
-  int64_t q, total;
-  int stage;
-};
+// A warp's slice of every row it visits, and the TMA ring that streams it.
+// The vocabulary is cut into warp-rows of 32 16-byte vectors; warp w owns a contiguous run of
+// warp-rows (balanced to within one), so only the very last warp-row of the vocabulary can be
+// ragged. Rows of the [T, V] matrix are visited round-robin over CTAs.
+template <int WARPS, int STAGES>
+struct WarpStream {
+  // static geometry
+  int sv, seg_len;        // first vector / number of vectors of this warp's slice
+  int64_t row_jump;       // bytes from the end of this slice in row r to its start in row r+grid
+  // producer (lane 0 issues, every lane tracks the same state)
+  const char* p_src;
+  int p_left, p_rows_left;
+  uint32_t p_dst, p_bar, ring_dst0, ring_bar0;
+  int p_stage;
+  uint64_t pol;
+  // consumer
+  uint32_t c_dst, c_bar;
+  int c_stage;
+  uint32_t c_par;
 
-// One TMA chunk (<= 256 16-B vectors) of the forward pass for one warp. FULL = all 8 vector
-// slots of every lane are live (no predication, no neutral fill).
-template <bool FULL, bool ENT, bool MINMAX, typename Refill>
-__device__ __forceinline__ void fwd_chunk(uint32_t base, int nv, int lane, float scale,
-                                          float& negm, float& s0, float& s1, float& t0,
-                                          float& t1, uint32_t& pmx, uint32_t& pmn,
-                                          Refill&& refill) {
-  uint4 v[8];
+  __device__ __forceinline__ void init(const void* base, int64_t ld_bytes, int V, int nrows,
+                                       unsigned char* my_data, uint64_t* my_bar, int warp,
+                                       int lane) {
+    const int nvec = V >> 3;
+    const int R = (nvec + 31) >> 5;
+    const int q = R / WARPS, rem = R % WARPS;
+    const int my_rows = q + (warp < rem ? 1 : 0);
+    sv = (warp * q + min(warp, rem)) * 32;
+    seg_len = max(0, min(my_rows * 32, nvec - sv));
+    row_jump = (int64_t)gridDim.x * ld_bytes - (int64_t)seg_len * 16;
+    p_src = reinterpret_cast<const char*>(base) + (int64_t)blockIdx.x * ld_bytes + (int64_t)sv * 16;
+    p_left = seg_len;
+    p_rows_left = seg_len > 0 ? nrows : 0;
+    ring_dst0 = smem_u32(my_data);
+    ring_bar0 = smem_u32(my_bar);
+    p_dst = c_dst = ring_dst0;
+    p_bar = c_bar = ring_bar0;
+    p_stage = c_stage = 0;
+    c_par = 0;
+    pol = policy_evict_first();
+    if (lane == 0) {
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    if (FULL || i * 32 + lane < nv) v[i] = lds128(base + i * 512);
-    else v[i] = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
-  }
-  refill();  // the slot is free again
-  // chunk maximum (packed bf16x2), lazy rescale of the lane's reference
-  uint32_t cm = max_bf16x2(max_bf16x2(v[0].x, v[0].y), max_bf16x2(v[0].z, v[0].w));
-#pragma unroll
-  for (int i = 1; i < 8; i++)
-    cm = max_bf16x2(cm, max_bf16x2(max_bf16x2(v[i].x, v[i].y), max_bf16x2(v[i].z, v[i].w)));
-  pmx = max_bf16x2(pmx, cm);
-  if (MINMAX) {
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-      if (FULL || i * 32 + lane < nv)
-        pmn = min_bf16x2(pmn, min_bf16x2(min_bf16x2(v[i].x, v[i].y), min_bf16x2(v[i].z, v[i].w)));
+      for (int s = 0; s < STAGES; s++) mbar_init(&my_bar[s], 1);
+      fence_barrier_init();
     }
-  }
-  const float cmf = fmaxf(bf16lo(cm), bf16hi(cm)) * scale;
-  if (cmf + negm > kRescaleThr) {
-    const float d = cmf + negm;  // new reference - old reference > 0
-    const float f = ex2_approx(-d);
-    const float s = s0 + s1, t = t0 + t1;
-    if (ENT) {
-      t0 = f * (t - d * s);
-      t1 = 0.f;
-    }
-    s0 = f * s;
-    s1 = 0.f;
-    negm = -cmf;
-  }
+    __syncwarp();
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const float y0 = fmaf(bf16lo(w[j]), scale, negm);
-      const float y1 = fmaf(bf16hi(w[j]), scale, negm);
-      const float e0 = ex2_approx(y0);
-      const float e1 = ex2_approx(y1);
-      s0 += e0;
-      s1 += e1;
-      if (ENT) {
-        t0 = fmaf(e0, y0, t0);
-        t1 = fmaf(e1, y1, t1);
+    for (int s = 0; s < STAGES; s++) issue(lane);
+  }
+
+  // Queue the next chunk of the slice into the next ring slot (no-op once all rows are queued).
+  __device__ __forceinline__ void issue(int lane) {
+    if (p_rows_left > 0) {
+      const int nv = min(kChunkVec, p_left);
+      const uint32_t bytes = (uint32_t)nv * 16u;
+      if (lane == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(p_bar), "r"(bytes)
+                     : "memory");
+        asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+            "[%0], [%1], %2, [%3], %4;" ::"r"(p_dst), "l"(p_src), "r"(bytes), "r"(p_bar), "l"(pol)
+            : "memory");
+      }
+      p_src += bytes;
+      p_left -= nv;
+      if (p_left == 0) {
+        p_left = seg_len;
+        p_src += row_jump;
+        p_rows_left--;
+      }
+      p_dst += kChunkBytes;
+      p_bar += 8;
+      if (++p_stage == STAGES) {
+        p_stage = 0;
+        p_dst = ring_dst0;
+        p_bar = ring_bar0;
       }
     }
   }
+
+  // Wait until the current consumer slot holds its chunk; returns its shared address.
+  __device__ __forceinline__ uint32_t wait() {
+    uint32_t ok;
+    do {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(ok)
+          : "r"(c_bar), "r"(c_par)
+          : "memory");
+    } while (!ok);
+    return c_dst;
+  }
+
+  // The warp has read the current slot into registers: hand it back to the producer.
+  // (generic-proxy reads followed by an async-proxy overwrite need no proxy fence; the
+  // __syncwarp orders every lane's reads before lane 0 issues the copy)
+  __device__ __forceinline__ void release(int lane) {
+    __syncwarp();
+    issue(lane);
+    c_dst += kChunkBytes;
+    c_bar += 8;
+    if (++c_stage == STAGES) {
+      c_stage = 0;
+      c_dst = ring_dst0;
+      c_bar = ring_bar0;
+      c_par ^= 1;
+    }
+  }
+};
+
+struct LaneState {
+  float negm, s0, s1, t0, t1;
+  uint32_t pmx, pmn;
+};
+
+template <bool ENT>
+__device__ __forceinline__ void lazy_rescale(LaneState& L, uint32_t cm, float scale) {
+  const float cmf = fmaxf(bf16lo(cm), bf16hi(cm)) * scale;
+  if (cmf + L.negm > kRescaleThr) {
+    const float d = cmf + L.negm;  // new reference - old reference > 0
+    const float f = ex2_approx(-d);
+    const float s = L.s0 + L.s1, t = L.t0 + L.t1;
+    if (ENT) {
+      L.t0 = f * (t - d * s);
+      L.t1 = 0.f;
+    }
+    L.s0 = f * s;
+    L.s1 = 0.f;
+    L.negm = -cmf;
+  }
+}
+
+template <bool ENT>
+__device__ __forceinline__ void accumulate_vec(LaneState& L, const uint4& v, float scale) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const float y0 = fmaf(bf16lo(w[j]), scale, L.negm);
+    const float y1 = fmaf(bf16hi(w[j]), scale, L.negm);
+    const float e0 = ex2_approx(y0);
+    const float e1 = ex2_approx(y1);
+    L.s0 += e0;
+    L.s1 += e1;
+    if (ENT) {
+      L.t0 = fmaf(e0, y0, L.t0);
+      L.t1 = fmaf(e1, y1, L.t1);
+    }
+  }
+}
+
+__device__ __forceinline__ uint32_t max4(const uint4& v) {
+  return max_bf16x2(max_bf16x2(v.x, v.y), max_bf16x2(v.z, v.w));
+}
+__device__ __forceinline__ uint32_t min4(const uint4& v) {
+  return min_bf16x2(min_bf16x2(v.x, v.y), min_bf16x2(v.z, v.w));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -122,189 +217,173 @@ logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FwdSmem<WARPS, STAGES>;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* my_data = smem + warp * STAGES * kChunkBytes;
-  uint64_t* my_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES;
-  float* part = reinterpret_cast<float*>(smem + L::kPartOff);  // [2][5][WARPS]
+  float* part = reinterpret_cast<float*>(smem + L::kPartOff);   // [kSlots][6][WARPS]
+  int* cnt = reinterpret_cast<int*>(smem + L::kCntOff);         // arrivals per slot
+  volatile int* gen = cnt + kSlots;                             // completed uses per slot
+  if (threadIdx.x < 2 * kSlots) cnt[threadIdx.x] = 0;
+  __syncthreads();
 
-  const int nvec = V >> 3;
-  const int seg = (nvec + WARPS - 1) / WARPS;
-  const int sv = warp * seg;
-  const int seg_len = max(0, min(seg, nvec - sv));
-  const int nck = (seg_len + kChunkVec - 1) / kChunkVec;
   const int nrows = (T - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  WarpStream<WARPS, STAGES> ws;
+  ws.init(logits, ld * 2, V, nrows, smem + warp * STAGES * kChunkBytes,
+          reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
 
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < STAGES; s++) mbar_init(&my_bar[s], 1);
-    fence_barrier_init();
-    fence_proxy_async();
-  }
-  __syncwarp();
-
-  const uint64_t pol = policy_evict_first();
-  Producer P{0, 0, 0, (int64_t)nrows * nck, 0};
-  auto issue = [&]() {  // lane 0 only
-    if (P.q < P.total) {
-      const int row = blockIdx.x + P.it * gridDim.x;
-      const int nv = min(kChunkVec, seg_len - P.ck * kChunkVec);
-      const char* src = reinterpret_cast<const char*>(logits) + ((int64_t)row * ld) * 2 +
-                        ((int64_t)(sv + P.ck * kChunkVec)) * 16;
-      mbar_expect_tx(&my_bar[P.stage], nv * 16);
-      bulk_g2s(my_data + P.stage * kChunkBytes, src, nv * 16, &my_bar[P.stage], pol);
-      P.q++;
-      if (++P.stage == STAGES) P.stage = 0;
-      if (++P.ck == nck) {
-        P.ck = 0;
-        P.it++;
-      }
-    }
-  };
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < STAGES; s++) issue();
-  }
-
-  auto refill = [&]() {  // called by all lanes once the chunk sits in registers
-    __syncwarp();
-    if (lane == 0) {
-      fence_proxy_async();
-      issue();
-    }
-  };
-
-  int c_stage = 0;
-  uint32_t c_par = 0;
   for (int it = 0; it < nrows; ++it) {
     const int row = blockIdx.x + it * gridDim.x;
-    // label logit: a single 2-byte gather, issued early by the finalising warp
+    // the label logit is a single 2-byte gather; one (rotating) warp fetches it early
     float xy = 0.f;
-    if (warp == 0 && lane == 0) {
+    const bool fetch_xy = (it % WARPS) == warp && lane == 0;
+    if (fetch_xy) {
       const int64_t lab = labels[row];
-      xy = (lab >= 0 && lab < V)
-               ? __bfloat162float(logits[(int64_t)row * ld + lab])
-               : __int_as_float(0x7fc00000);
+      xy = (lab >= 0 && lab < V) ? __bfloat162float(logits[(int64_t)row * ld + lab])
+                                 : __int_as_float(0x7fc00000);
     }
-    float negm = kSentinel;  // minus the lane's reference exponent (log2 domain)
-    float s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f;
-    uint32_t pmx = kNegInf2, pmn = kPosInf2;
+    LaneState S{kSentinel, 0.f, 0.f, 0.f, 0.f, kNegInf2, kPosInf2};
 
-    for (int ck = 0; ck < nck; ++ck) {
-      const int nv = min(kChunkVec, seg_len - ck * kChunkVec);
-      mbar_wait(&my_bar[c_stage], c_par);
-      const uint32_t base = smem_u32(my_data + c_stage * kChunkBytes) + lane * 16;
-      if (nv == kChunkVec)
-        fwd_chunk<true, ENT, MINMAX>(base, nv, lane, scale, negm, s0, s1, t0, t1, pmx, pmn, refill);
-      else
-        fwd_chunk<false, ENT, MINMAX>(base, nv, lane, scale, negm, s0, s1, t0, t1, pmx, pmn, refill);
-      if (++c_stage == STAGES) {
-        c_stage = 0;
-        c_par ^= 1;
+    int left = ws.seg_len;
+    while (left > 0) {
+      const int nv = min(kChunkVec, left);
+      left -= nv;
+      const uint32_t base = ws.wait() + lane * 16;
+      if (nv == kChunkVec) {
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
+        ws.release(lane);
+        uint32_t cm = max4(v[0]);
+#pragma unroll
+        for (int i = 1; i < 8; i++) cm = max_bf16x2(cm, max4(v[i]));
+        S.pmx = max_bf16x2(S.pmx, cm);
+        if (MINMAX) {
+#pragma unroll
+          for (int i = 0; i < 8; i++) S.pmn = min_bf16x2(S.pmn, min4(v[i]));
+        }
+        lazy_rescale<ENT>(S, cm, scale);
+#pragma unroll
+        for (int i = 0; i < 8; i++) accumulate_vec<ENT>(S, v[i], scale);
+      } else {
+        // tail of the slice: 1..7 warp-rows, only the vocabulary's last one can be ragged
+        const int nr = (nv + 31) >> 5;
+#pragma unroll 1
+        for (int r = 0; r < nr; r++) {
+          const bool act = r * 32 + lane < nv;
+          uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
+          if (act) v = lds128(base + r * 512);
+          const uint32_t cm = max4(v);
+          S.pmx = max_bf16x2(S.pmx, cm);
+          if (MINMAX && act) S.pmn = min_bf16x2(S.pmn, min4(v));
+          lazy_rescale<ENT>(S, cm, scale);
+          accumulate_vec<ENT>(S, v, scale);
+        }
+        ws.release(lane);
       }
     }
 
     // ---- combine the 32 lanes of this warp -------------------------------------------------
-    {
-      const float m = -negm;
-      const float s = s0 + s1, t = t0 + t1;
-      const float M = warp_max(m);
-      const float dl = m - M;  // <= 0
-      const float f = ex2_approx(dl);
-      const float S = warp_sum(s * f);
-      float Tt = 0.f;
-      if (ENT) Tt = warp_sum(f * fmaf(dl, s, t));
-      float mx = 0.f, mn = 0.f;
-      if (MINMAX) {
-        mx = warp_max(fmaxf(bf16lo(pmx), bf16hi(pmx)));
-        mn = warp_min(fminf(bf16lo(pmn), bf16hi(pmn)));
-      }
-      if (lane == 0) {
-        float* p = part + (it & 1) * 5 * WARPS;
-        p[0 * WARPS + warp] = M;
-        p[1 * WARPS + warp] = S;
-        p[2 * WARPS + warp] = Tt;
-        p[3 * WARPS + warp] = mx;
-        p[4 * WARPS + warp] = mn;
-      }
+    const float m = -S.negm;
+    const float s = S.s0 + S.s1, t = S.t0 + S.t1;
+    const float M = warp_max(m);
+    const float dl = m - M;  // <= 0
+    const float f = ex2_approx(dl);
+    const float Ssum = warp_sum(s * f);
+    float Tt = 0.f;
+    if (ENT) Tt = warp_sum(f * fmaf(dl, s, t));
+    float mx = 0.f, mn = 0.f;
+    if (MINMAX) {
+      mx = warp_max(fmaxf(bf16lo(S.pmx), bf16hi(S.pmx)));
+      mn = warp_min(fminf(bf16lo(S.pmn), bf16hi(S.pmn)));
     }
-    __syncthreads();
-    if (warp == 0) {
-      const float* p = part + (it & 1) * 5 * WARPS;
+    // ---- publish; the last warp to arrive finalises the row (no CTA-wide barrier) -----------
+    const int slot = it & (kSlots - 1);
+    const int use = it / kSlots;
+    float* p = part + slot * 6 * WARPS;
+    int old = 0;
+    if (lane == 0) {
+      while (gen[slot] < use) {  // slot still being read for row it - kSlots (rare)
+      }
+      p[0 * WARPS + warp] = M;
+      p[1 * WARPS + warp] = Ssum;
+      p[2 * WARPS + warp] = Tt;
+      p[3 * WARPS + warp] = mx;
+      p[4 * WARPS + warp] = mn;
+      if (fetch_xy) p[5 * WARPS] = xy;
+      __threadfence_block();
+      old = atomicAdd(&cnt[slot], 1);
+    }
+    old = __shfl_sync(0xffffffffu, old, 0);
+    if (old == WARPS - 1) {
+      __threadfence_block();
+      const volatile float* q = p;
       const bool has = lane < WARPS;
-      const float Mw = has ? p[0 * WARPS + lane] : -kSentinel;
-      const float Sw = has ? p[1 * WARPS + lane] : 0.f;
-      const float Tw = has ? p[2 * WARPS + lane] : 0.f;
-      const float M = warp_max(Mw);
-      const float dl = Mw - M;
-      const float f = ex2_approx(dl);
-      const float S = warp_sum(Sw * f);
-      float Tt = 0.f;
-      if (ENT) Tt = warp_sum(f * fmaf(dl, Sw, Tw));
-      float mx = 0.f, mn = 0.f;
+      const float Mw = has ? q[0 * WARPS + lane] : -kSentinel;
+      const float Sw = has ? q[1 * WARPS + lane] : 0.f;
+      const float Tw = has ? q[2 * WARPS + lane] : 0.f;
+      const float mxw = has ? q[3 * WARPS + lane] : -INFINITY;
+      const float mnw = has ? q[4 * WARPS + lane] : INFINITY;
+      const float xyr = q[5 * WARPS];
+      const float Mr = warp_max(Mw);
+      const float dr = Mw - Mr;
+      const float fr = ex2_approx(dr);
+      const float Sr = warp_sum(Sw * fr);
+      float Tr = 0.f;
+      if (ENT) Tr = warp_sum(fr * fmaf(dr, Sw, Tw));
+      float mxr = 0.f, mnr = 0.f;
       if (MINMAX) {
-        mx = warp_max(has ? p[3 * WARPS + lane] : -INFINITY);
-        mn = warp_min(has ? p[4 * WARPS + lane] : INFINITY);
+        mxr = warp_max(mxw);
+        mnr = warp_min(mnw);
       }
       if (lane == 0) {
-        const float l2s = log2f(S);
-        const float lse2 = M + l2s;  // log2 domain
-        lse[row] = lse2 * kLn2;
+        cnt[slot] = 0;
+        const float l2s = log2f(Sr);
+        lse[row] = (Mr + l2s) * kLn2;
         // (x_y*scale - M) first: exact cancellation when the label is the row maximum, however
         // large |M| is; only then the (small) log2 of the sum
-        logp[row] = (fmaf(xy, scale, -M) - l2s) * kLn2;
-        if (ENT) ent[row] = kLn2 * (l2s - Tt / S);
+        logp[row] = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
+        if (ENT) ent[row] = kLn2 * (l2s - Tr / Sr);
         if (MINMAX) {
-          if (rowmax) rowmax[row] = mx;
-          if (rowmin) rowmin[row] = mn;
+          if (rowmax) rowmax[row] = mxr;
+          if (rowmin) rowmin[row] = mnr;
         }
+        __threadfence_block();
+        gen[slot] = use + 1;
       }
     }
   }
 }
 
-// One TMA chunk of the backward pass for one warp.
-template <bool FULL, bool HAS_GH, typename Refill>
-__device__ __forceinline__ void bwd_chunk(uint32_t base, int nv, int lane, int v0, float scale,
-                                          float nlse2, float A0, float B0, float lab_add,
-                                          int lvec, int lsub, char* out_row, Refill&& refill) {
-  uint4 v[8];
+// One warp-row group (8 vectors per lane) of the backward pass.
+template <bool HAS_GH>
+__device__ __forceinline__ void bwd_vec(const uint4& v, int vi, bool act, float scale, float nlse2,
+                                        float A0, float B0, float lab_add, int lvec, int lsub,
+                                        char* out_row) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  float d[8];
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    if (FULL || i * 32 + lane < nv) v[i] = lds128(base + i * 512);
-    else v[i] = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
+  for (int j = 0; j < 4; j++) {
+    const float y0 = fmaf(bf16lo(w[j]), scale, nlse2);
+    const float y1 = fmaf(bf16hi(w[j]), scale, nlse2);
+    const float p0 = ex2_approx(y0);
+    const float p1 = ex2_approx(y1);
+    if (HAS_GH) {
+      d[2 * j] = p0 * fmaf(B0, y0, A0);
+      d[2 * j + 1] = p1 * fmaf(B0, y1, A0);
+    } else {
+      d[2 * j] = p0 * A0;
+      d[2 * j + 1] = p1 * A0;
+    }
   }
-  refill();
+  if (vi == lvec) {  // the one-hot term of the label, one lane once per row
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-    float d[8];
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const float y0 = fmaf(bf16lo(w[j]), scale, nlse2);
-      const float y1 = fmaf(bf16hi(w[j]), scale, nlse2);
-      const float p0 = ex2_approx(y0);
-      const float p1 = ex2_approx(y1);
-      if (HAS_GH) {
-        d[2 * j] = p0 * fmaf(B0, y0, A0);
-        d[2 * j + 1] = p1 * fmaf(B0, y1, A0);
-      } else {
-        d[2 * j] = p0 * A0;
-        d[2 * j + 1] = p1 * A0;
-      }
-    }
-    const int vi = v0 + i * 32;
-    if (vi == lvec) {  // the one-hot term of the label, one lane once per row
-#pragma unroll
-      for (int k = 0; k < 8; k++)
-        if (k == lsub) d[k] += lab_add;
-    }
-    if (FULL || i * 32 + lane < nv) {
-      uint4 o;
-      o.x = pack_bf16x2(d[0], d[1]);
-      o.y = pack_bf16x2(d[2], d[3]);
-      o.z = pack_bf16x2(d[4], d[5]);
-      o.w = pack_bf16x2(d[6], d[7]);
-      stg_na_v4(out_row + (int64_t)vi * 16, o);
-    }
+    for (int k = 0; k < 8; k++)
+      if (k == lsub) d[k] += lab_add;
+  }
+  if (act) {
+    uint4 o;
+    o.x = pack_bf16x2(d[0], d[1]);
+    o.y = pack_bf16x2(d[2], d[3]);
+    o.z = pack_bf16x2(d[4], d[5]);
+    o.w = pack_bf16x2(d[6], d[7]);
+    stg_na_v4(out_row + (int64_t)vi * 16, o);
   }
 }
 
@@ -321,55 +400,11 @@ logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FwdSmem<WARPS, STAGES>;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* my_data = smem + warp * STAGES * kChunkBytes;
-  uint64_t* my_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES;
-
-  const int nvec = V >> 3;
-  const int seg = (nvec + WARPS - 1) / WARPS;
-  const int sv = warp * seg;
-  const int seg_len = max(0, min(seg, nvec - sv));
-  const int nck = (seg_len + kChunkVec - 1) / kChunkVec;
   const int nrows = (T - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-  if (nck == 0) return;  // this warp owns no part of the row (tiny vocabularies)
-
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < STAGES; s++) mbar_init(&my_bar[s], 1);
-    fence_barrier_init();
-    fence_proxy_async();
-  }
-  __syncwarp();
-
-  const uint64_t pol = policy_evict_first();
-  Producer P{0, 0, 0, (int64_t)nrows * nck, 0};
-  auto issue = [&]() {
-    if (P.q < P.total) {
-      const int row = blockIdx.x + P.it * gridDim.x;
-      const int nv = min(kChunkVec, seg_len - P.ck * kChunkVec);
-      const char* src = reinterpret_cast<const char*>(logits) + ((int64_t)row * ld) * 2 +
-                        ((int64_t)(sv + P.ck * kChunkVec)) * 16;
-      mbar_expect_tx(&my_bar[P.stage], nv * 16);
-      bulk_g2s(my_data + P.stage * kChunkBytes, src, nv * 16, &my_bar[P.stage], pol);
-      P.q++;
-      if (++P.stage == STAGES) P.stage = 0;
-      if (++P.ck == nck) {
-        P.ck = 0;
-        P.it++;
-      }
-    }
-  };
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < STAGES; s++) issue();
-  }
-
-  auto refill = [&]() {
-    __syncwarp();
-    if (lane == 0) {
-      fence_proxy_async();
-      issue();
-    }
-  };
+  WarpStream<WARPS, STAGES> ws;
+  ws.init(logits, ld * 2, V, nrows, smem + warp * STAGES * kChunkBytes,
+          reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
+  if (ws.seg_len == 0) return;  // this warp owns no part of the row (tiny vocabularies)
 
   // per-row constants, fetched one row ahead
   auto load_row = [&](int row, float& nlse2, float& A0, float& B0, float& lab_add, int& lvec,
@@ -393,8 +428,6 @@ logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
   int n_lvec = -1, n_lsub = 0;
   if (nrows > 0) load_row(blockIdx.x, n_nlse2, n_A0, n_B0, n_lab, n_lvec, n_lsub);
 
-  int c_stage = 0;
-  uint32_t c_par = 0;
   for (int it = 0; it < nrows; ++it) {
     const int row = blockIdx.x + it * gridDim.x;
     const float nlse2 = n_nlse2, A0 = n_A0, B0 = n_B0, lab_add = n_lab;
@@ -402,19 +435,32 @@ logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
     if (it + 1 < nrows) load_row(row + gridDim.x, n_nlse2, n_A0, n_B0, n_lab, n_lvec, n_lsub);
     char* out_row = reinterpret_cast<char*>(dlogits) + ((int64_t)row * ld_out) * 2;
 
-    for (int ck = 0; ck < nck; ++ck) {
-      const int nv = min(kChunkVec, seg_len - ck * kChunkVec);
-      mbar_wait(&my_bar[c_stage], c_par);
-      const uint32_t base = smem_u32(my_data + c_stage * kChunkBytes) + lane * 16;
-      const int v0 = sv + ck * kChunkVec + lane;  // global 16-B vector index of slot 0
-      if (nv == kChunkVec)
-        bwd_chunk<true, HAS_GH>(base, nv, lane, v0, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row, refill);
-      else
-        bwd_chunk<false, HAS_GH>(base, nv, lane, v0, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row, refill);
-      if (++c_stage == STAGES) {
-        c_stage = 0;
-        c_par ^= 1;
+    int left = ws.seg_len;
+    int v0 = ws.sv + lane;  // global 16-B vector index of this lane's first vector in the chunk
+    while (left > 0) {
+      const int nv = min(kChunkVec, left);
+      left -= nv;
+      const uint32_t base = ws.wait() + lane * 16;
+      if (nv == kChunkVec) {
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
+        ws.release(lane);
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+          bwd_vec<HAS_GH>(v[i], v0 + i * 32, true, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+      } else {
+        const int nr = (nv + 31) >> 5;
+#pragma unroll 1
+        for (int r = 0; r < nr; r++) {
+          const bool act = r * 32 + lane < nv;
+          uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
+          if (act) v = lds128(base + r * 512);
+          bwd_vec<HAS_GH>(v, v0 + r * 32, act, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+        }
+        ws.release(lane);
       }
+      v0 += kChunkVec;
     }
   }
 }

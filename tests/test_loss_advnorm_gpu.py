@@ -84,8 +84,8 @@ def test_loss_vs_oracle_ties_and_sizes(cuda):
         prox = -torch.rand(T, generator=gen) * 2
         lp = prox.clone()
         lp[1::4] += 0.5 * torch.randn(T, generator=gen)[1::4]
-        lp[2::4] += np.log(1.2)   # on the upper bound (up to rounding)
-        lp[3::4] += np.log(0.8)
+        lp[2::4] += np.log(1.2) + 0.01   # just outside the upper bound
+        lp[3::4] += np.log(0.8) - 0.01   # just outside the lower bound
         old = prox + 0.1 * torch.randn(T, generator=gen)
         adv = torch.randn(T, generator=gen)
         adv[::7] = 0.0
@@ -105,6 +105,21 @@ def test_loss_vs_oracle_ties_and_sizes(cuda):
                     assert torch.equal(s_g[key].cpu(), s_r[key]), key
                 else:
                     np.testing.assert_allclose(s_g[key].cpu().numpy(), s_r[key].numpy(), rtol=1e-5, atol=1e-6)
+    # exact ties: lp == prox gives ratio == 1.0 on both sides; with eps_clip = 0 the ratio sits ON both
+    # clamp bounds (inclusive -> gradient passes) and pg_loss1 == pg_loss2 (max splits 1/2 + 1/2)
+    T = 64
+    gen = torch.Generator().manual_seed(1)
+    prox = -torch.rand(T, generator=gen)
+    adv = torch.randn(T, generator=gen)
+    mask = torch.ones(T, dtype=torch.bool)
+    a = prox.clone().requires_grad_(True)
+    l_r, _ = torch_ref.ppo_actor_loss(a, prox, prox, adv, 0.0, mask, c_clip=1.5)
+    l_r.backward()
+    b = prox.clone().to(cuda).requires_grad_(True)
+    l_g, _ = BF.ppo_actor_loss_fn(b, prox.to(cuda), prox.to(cuda), adv.to(cuda), 0.0, mask.to(cuda), c_clip=1.5)
+    l_g.backward()
+    np.testing.assert_allclose(b.grad.cpu().numpy(), a.grad.numpy(), rtol=1e-6, atol=0)
+    assert float(a.grad.abs().sum()) > 0
     # 2-D inputs keep their shape
     x = torch.randn(4, 9, device=cuda)
     l, s = BF.ppo_actor_loss_fn(x, x, x, x, 0.2, torch.ones(4, 9, dtype=torch.bool, device=cuda))
