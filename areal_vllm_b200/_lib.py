@@ -50,6 +50,11 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int64,
          c_float, c_float, c_int, c_void_p, c_size_t, c_void_p],
     ),
+    "b200rl_gae_1d_nolp_misalign_noalloc": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int64,
+         c_float, c_float, c_void_p],
+    ),
     "b200rl_ppo_loss_workspace_bytes": (c_size_t, [c_int64]),
     "b200rl_ppo_loss_fwd": (
         c_int,

@@ -434,3 +434,83 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
 }
 
 }  // extern "C"
+
+// =============================================================================================
+// Allocation-free variant of the tiled scan.
+//
+// Who needs it: a process that shares its GPU with an inference server which has already
+// reserved nearly all of HBM for its KV cache (the usual AReaL colocated layout), a plain C / FFI
+// host that has no device allocator of its own to hand us a workspace from, or any caller that
+// runs at a point where device allocation is forbidden or may fail. For those callers the look-back
+// state of gae_scan_kernel lives in the library image instead of in a caller buffer: every GPU that
+// loads libb200rl.so carries this array (about 33 KB) until the process exits.
+//
+// The array below is named from HOST code only to ask the runtime where it lives
+// (cudaGetSymbolAddress); the name itself is not a device pointer and must never be passed to a
+// kernel. The lookup happens once per device, on that device, the first time the entry point is
+// called there.
+// =============================================================================================
+namespace b200rl {
+namespace {
+constexpr int64_t kNoAllocMaxTokens = 4194304;  // 4 Mi packed tokens = 4096 tiles
+constexpr size_t kNoAllocBytes = 256 + ((size_t)(kNoAllocMaxTokens / kTile) + 1) * sizeof(uint64_t);
+constexpr size_t kNoAllocBytesPadded = (kNoAllocBytes + 255) & ~(size_t)255;
+}  // namespace
+}  // namespace b200rl
+
+static __device__ __align__(256) unsigned char g_gae_noalloc_scratch[b200rl::kNoAllocBytesPadded];
+
+namespace b200rl {
+namespace {
+// Device address of the scratch array on the CURRENT device (resolved and cached on first use).
+int gae_noalloc_scratch(void** out) {
+  static void* resolved[64] = {nullptr};
+  int dev = 0;
+  B200RL_CUDA(cudaGetDevice(&dev));
+  B200RL_REQUIRE(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+  if (resolved[dev] == nullptr) {
+    void* p = nullptr;
+    B200RL_CUDA(cudaGetSymbolAddress((void**)&p, g_gae_noalloc_scratch));
+    B200RL_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    B200RL_CUDA(cudaFuncSetAttribute(gae_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(sizeof(ScanSmem) * kScanWarps)));
+    resolved[dev] = p;
+  }
+  *out = resolved[dev];
+  return B200RL_OK;
+}
+}  // namespace
+}  // namespace b200rl
+
+extern "C" int b200rl_gae_1d_nolp_misalign_noalloc(const float* rewards, const float* values,
+                                                   const int32_t* cu_seqlens,
+                                                   const uint8_t* bootstrap, float* adv, float* ret,
+                                                   int32_t batch, int64_t total, float gamma,
+                                                   float lam, void* stream) {
+  using namespace b200rl;
+  B200RL_REQUIRE(batch >= 0 && total >= 0, "negative size");
+  if (total > kNoAllocMaxTokens) {
+    set_last_error(
+        "b200rl_gae_1d_nolp_misalign_noalloc: %lld tokens exceed the built-in scratch, which covers "
+        "at most %lld; call b200rl_gae_1d_nolp_misalign with a caller-provided workspace instead",
+        (long long)total, (long long)kNoAllocMaxTokens);
+    return B200RL_EINVAL;
+  }
+  if (batch == 0 || total == 0) return B200RL_OK;
+  B200RL_REQUIRE(rewards && values && cu_seqlens && bootstrap && adv && ret, "null pointer");
+  void* scratch = nullptr;
+  int rc = gae_noalloc_scratch(&scratch);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  ScanWs W = scan_ws(scratch, total);
+  // the array keeps whatever the previous call left: ticket counter and tile states must be zero
+  B200RL_CUDA(cudaMemsetAsync(scratch, 0, W.bytes, st));
+  int grid = (W.num_tiles + kScanWarps - 1) / kScanWarps;
+  const int cap = sm_count() * 4;
+  if (grid > cap) grid = cap;
+  gae_scan_kernel<<<grid, kScanWarps * 32, sizeof(ScanSmem) * kScanWarps, st>>>(
+      rewards, values, cu_seqlens, bootstrap, adv, ret, batch, (int)total, gamma, lam, W.state,
+      W.ticket, W.num_tiles);
+  return check_launch("gae_scan_kernel (noalloc)");
+}
+

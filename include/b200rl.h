@@ -87,6 +87,26 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
                                 float* ret, int32_t batch, int64_t total, float gamma, float lam,
                                 int mode, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Same computation as b200rl_gae_1d_nolp_misalign in SCAN mode, for callers that cannot give the
+ * library a workspace: e.g. a trainer colocated with an inference server that has already claimed
+ * nearly all of HBM, or a bare C / FFI host with no device allocator of its own. This entry point
+ * has no counterpart in the reference. It performs no device allocation of any kind: the tile
+ * look-back state lives in a fixed array inside the library image (about 33 KB, resident on every
+ * GPU that loads the library until the process exits). The caller still owns all inputs and outputs.
+ *  - Limit: total <= 4,194,304 packed tokens; larger inputs are refused with B200RL_EINVAL and a
+ *    message pointing at the workspace variant.
+ *  - The first call on each device looks up the array's device address (one-time set-up with that
+ *    device current). Make that first call before starting any stream capture.
+ *  - All calls on a device share the one array and each call clears the part it uses, so two calls
+ *    that may overlap on the GPU (different streams, or different threads) race with each other:
+ *    serialise them on one stream.
+ *  - Numerics are those of SCAN (see above): fp32 additions are re-associated, so for
+ *    gamma*lam > 0.99 results can leave the 1e-5 band around the reference's serial order. */
+int b200rl_gae_1d_nolp_misalign_noalloc(const float* rewards, const float* values,
+                                        const int32_t* cu_seqlens, const uint8_t* bootstrap,
+                                        float* adv, float* ret, int32_t batch, int64_t total,
+                                        float gamma, float lam, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * H2  clipped PPO / GRPO actor loss with decoupled-PPO behaviour weights.
  * ref: areal/utils/functional.py:124-188 (ppo_actor_loss_fn);
