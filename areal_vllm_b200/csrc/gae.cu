@@ -84,18 +84,26 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
       __syncwarp();
       if (lane == 0) {
         int q = cnt - 1;
-        // tail down to a multiple of 4, then 4 at a time with 16-B smem accesses
+        // ragged top down to a multiple of 4, then 4 tokens per step with 16-B smem accesses; the
+        // next group is loaded before the current one is chained, so only the 4 dependent FMAs
+        // (4 cycles each) sit on the critical path
         for (; (q & 3) != 3 && q >= 0; q--) {
           X = __fmaf_rn(c, X, d[q]);
           d[q] = X;
         }
-        for (; q >= 3; q -= 4) {
-          float4 t = *reinterpret_cast<float4*>(d + q - 3);
-          t.w = X = __fmaf_rn(c, X, t.w);
-          t.z = X = __fmaf_rn(c, X, t.z);
-          t.y = X = __fmaf_rn(c, X, t.y);
-          t.x = X = __fmaf_rn(c, X, t.x);
-          *reinterpret_cast<float4*>(d + q - 3) = t;
+        if (q >= 3) {
+          float4 cur = *reinterpret_cast<float4*>(d + q - 3);
+#pragma unroll 4
+          for (; q >= 3; q -= 4) {
+            float4 nxt = cur;
+            if (q >= 7) nxt = *reinterpret_cast<float4*>(d + q - 7);
+            cur.w = X = __fmaf_rn(c, X, cur.w);
+            cur.z = X = __fmaf_rn(c, X, cur.z);
+            cur.y = X = __fmaf_rn(c, X, cur.y);
+            cur.x = X = __fmaf_rn(c, X, cur.x);
+            *reinterpret_cast<float4*>(d + q - 3) = cur;
+            cur = nxt;
+          }
         }
       }
       __syncwarp();
@@ -235,22 +243,30 @@ gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ val
     __syncwarp();
 
     // ---- load (coalesced, lane-strided) and delta ---------------------------------------
-#pragma unroll 2
-    for (int k = 0; k < kTile / 32; k++) {
-      const int o = k * 32 + lane;
-      if (o < tlen) {
+    // 8 lane-strided rows at a time: 24 independent global loads in flight per lane
+#pragma unroll 1
+    for (int kb = 0; kb < kTile / 32; kb += 8) {
+      float rr[8], vv[8], nn[8];
+      int mm[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const int o = (kb + j) * 32 + lane;
+        const bool ok = o < tlen;
+        mm[j] = ok ? S.meta[o] : 0;
         const int t = tlo + o;
-        const int m = S.meta[o];
-        const int64_t vi = (int64_t)t + i_lo + (m & kMetaCnt);
-        const float r = rewards[t];
-        const float v = values[vi];
-        float nv = values[vi + 1];
-        if ((m & kMetaLast) && !(m & kMetaBoot)) nv = 0.f;
-        S.d[o] = fmaf(gamma, nv, r) - v;
-        S.v[o] = v;
-      } else {
-        S.d[o] = 0.f;
-        S.meta[o] = 0;
+        const int64_t vi = (int64_t)t + i_lo + (mm[j] & kMetaCnt);
+        rr[j] = ok ? rewards[t] : 0.f;
+        vv[j] = ok ? values[vi] : 0.f;
+        nn[j] = ok ? values[vi + 1] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const int o = (kb + j) * 32 + lane;
+        float nv = nn[j];
+        if ((mm[j] & kMetaLast) && !(mm[j] & kMetaBoot)) nv = 0.f;
+        S.d[o] = (o < tlen) ? fmaf(gamma, nv, rr[j]) - vv[j] : 0.f;
+        S.v[o] = vv[j];
+        if (o >= tlen) S.meta[o] = 0;
       }
     }
     __syncwarp();

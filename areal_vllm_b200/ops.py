@@ -2,7 +2,13 @@
 
 Each op validates, allocates outputs/workspace with torch (plumbing only) and launches exactly
 the C-ABI entry point on the current CUDA stream. Fake (meta) implementations are registered so
-the ops trace under torch.compile / CUDA-graph capture; none of them synchronises with the host.
+the ops trace under torch.compile; none of them synchronises with the host.
+
+Two ways in, one implementation: the ``b200rl::*`` custom ops (``*_op`` below; what a compiled
+graph sees) and, for eager mode, plain functions of the same names without the ``_op`` suffix that
+call the same launchers directly — through ``torch.autograd.Function`` where a gradient exists —
+because the dispatcher round trip of a python custom op costs 50-150 us per call, which is more
+than the [T]-sized kernels themselves take.
 """
 
 from __future__ import annotations
@@ -15,6 +21,26 @@ from . import _lib
 from ._lib import check, lib, ptr, stream_handle
 
 Tensor = torch.Tensor
+
+
+class _NullCtx:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
+
+
+_NULL = _NullCtx()
+
+
+def _on(dev: torch.device):
+    """Context that makes `dev` current for the launch (free when it already is)."""
+    return _NULL if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
+
+
+def _eager() -> bool:
+    return not torch.compiler.is_compiling()
 
 
 # --------------------------------------------------------------------------------------------
@@ -36,8 +62,7 @@ def _check_logits(logits: Tensor, labels: Tensor) -> None:
         raise RuntimeError("labels must be contiguous")
 
 
-@torch.library.custom_op("b200rl::logprob_entropy_fwd", mutates_args=())
-def logprob_entropy_fwd(
+def _raw_logprob_entropy_fwd(
     logits: Tensor, labels: Tensor, temperature: float, need_entropy: bool, need_minmax: bool
 ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
     """-> (logp[T], entropy[T] or empty, lse[T], rowmax[T] or empty, rowmin[T] or empty), all fp32."""
@@ -50,7 +75,7 @@ def logprob_entropy_fwd(
     ent = torch.empty(T if need_entropy else 0, **f32)
     rmax = torch.empty(T if need_minmax else 0, **f32)
     rmin = torch.empty(T if need_minmax else 0, **f32)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_logprob_entropy_fwd(
             ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
             ptr(labels), T, V, float(temperature), ptr(logp),
@@ -62,15 +87,17 @@ def logprob_entropy_fwd(
     return logp, ent, lse, rmax, rmin
 
 
-@logprob_entropy_fwd.register_fake
+logprob_entropy_fwd_op = torch.library.custom_op("b200rl::logprob_entropy_fwd", _raw_logprob_entropy_fwd, mutates_args=())
+
+
+@logprob_entropy_fwd_op.register_fake
 def _(logits, labels, temperature, need_entropy, need_minmax):
     T = logits.shape[0]
     mk = lambda n: logits.new_empty((n,), dtype=torch.float32)
     return mk(T), mk(T if need_entropy else 0), mk(T), mk(T if need_minmax else 0), mk(T if need_minmax else 0)
 
 
-@torch.library.custom_op("b200rl::logprob_entropy_bwd", mutates_args=())
-def logprob_entropy_bwd(
+def _raw_logprob_entropy_bwd(
     logits: Tensor, labels: Tensor, lse: Tensor, entropy: Tensor, g_logp: Tensor,
     g_ent: Optional[Tensor], temperature: float,
 ) -> Tensor:
@@ -84,7 +111,7 @@ def logprob_entropy_bwd(
         if entropy.numel() != T:
             raise RuntimeError("entropy gradient given but the forward did not compute the entropy")
     dlogits = torch.empty((T, V), dtype=logits.dtype, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_logprob_entropy_bwd(
             ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
             ptr(labels), ptr(lse), ptr(entropy) if g_ent is not None else None, ptr(g_logp),
@@ -94,7 +121,10 @@ def logprob_entropy_bwd(
     return dlogits
 
 
-@logprob_entropy_bwd.register_fake
+logprob_entropy_bwd_op = torch.library.custom_op("b200rl::logprob_entropy_bwd", _raw_logprob_entropy_bwd, mutates_args=())
+
+
+@logprob_entropy_bwd_op.register_fake
 def _(logits, labels, lse, entropy, g_logp, g_ent, temperature):
     return logits.new_empty(logits.shape)
 
@@ -112,20 +142,58 @@ def _lp_backward(ctx, g_logp, g_ent, g_lse, g_max, g_min):
     if g_logp is None:
         g_logp = torch.zeros_like(lse)
     use_ent = ctx.need_entropy and g_ent is not None
-    dlogits = logprob_entropy_bwd(
+    dlogits = logprob_entropy_bwd_op(
         logits, labels, lse, ent, g_logp, g_ent if use_ent else None, ctx.temperature
     )
     return dlogits, None, None, None, None
 
 
-logprob_entropy_fwd.register_autograd(_lp_backward, setup_context=_lp_setup_context)
+logprob_entropy_fwd_op.register_autograd(_lp_backward, setup_context=_lp_setup_context)
+
+
+class _LogprobFn(torch.autograd.Function):
+    """Eager-mode autograd node: same launchers as the custom op, no dispatcher round trip."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, temperature, need_entropy, need_minmax):
+        out = _raw_logprob_entropy_fwd(logits, labels, temperature, need_entropy, need_minmax)
+        ctx.save_for_backward(logits, labels, out[2], out[1])
+        ctx.temperature = temperature
+        ctx.need_entropy = need_entropy
+        ctx.set_materialize_grads(False)  # an unused entropy must arrive as None, not zeros
+        ctx.mark_non_differentiable(out[2], out[3], out[4])
+        return out
+
+    @staticmethod
+    def backward(ctx, g_logp, g_ent, g_lse, g_max, g_min):
+        logits, labels, lse, ent = ctx.saved_tensors
+        if g_logp is None:
+            g_logp = torch.zeros_like(lse)
+        use_ent = ctx.need_entropy and g_ent is not None
+        dlogits = _raw_logprob_entropy_bwd(
+            logits, labels, lse, ent, g_logp, g_ent if use_ent else None, ctx.temperature
+        )
+        return dlogits, None, None, None, None
+
+
+def logprob_entropy_fwd(logits, labels, temperature, need_entropy, need_minmax):
+    if not _eager():
+        return logprob_entropy_fwd_op(logits, labels, temperature, need_entropy, need_minmax)
+    if logits.requires_grad and torch.is_grad_enabled():
+        return _LogprobFn.apply(logits, labels, temperature, need_entropy, need_minmax)
+    return _raw_logprob_entropy_fwd(logits, labels, temperature, need_entropy, need_minmax)
+
+
+def logprob_entropy_bwd(logits, labels, lse, entropy, g_logp, g_ent, temperature):
+    if not _eager():
+        return logprob_entropy_bwd_op(logits, labels, lse, entropy, g_logp, g_ent, temperature)
+    return _raw_logprob_entropy_bwd(logits, labels, lse, entropy, g_logp, g_ent, temperature)
 
 
 # --------------------------------------------------------------------------------------------
 # H3 GAE
 # --------------------------------------------------------------------------------------------
-@torch.library.custom_op("b200rl::gae_1d_nolp_misalign", mutates_args=())
-def gae_1d_nolp_misalign(
+def _raw_gae_1d_nolp_misalign(
     rewards: Tensor, values: Tensor, cu_seqlens: Tensor, bootstrap: Tensor, gamma: float,
     lam: float, mode: int,
 ) -> Tuple[Tensor, Tensor]:
@@ -153,7 +221,7 @@ def gae_1d_nolp_misalign(
         return adv, ret
     ws_bytes = lib.b200rl_gae_workspace_bytes(batch, total)
     ws = _lib.workspace(ws_bytes, dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_gae_1d_nolp_misalign(
             ptr(rewards), ptr(values), ptr(cu_seqlens), ptr(bootstrap), ptr(adv), ptr(ret),
             batch, total, float(gamma), float(lam), int(mode), ptr(ws), ws.numel(),
@@ -163,16 +231,24 @@ def gae_1d_nolp_misalign(
     return adv, ret
 
 
-@gae_1d_nolp_misalign.register_fake
+gae_1d_nolp_misalign_op = torch.library.custom_op("b200rl::gae_1d_nolp_misalign", _raw_gae_1d_nolp_misalign, mutates_args=())
+
+
+@gae_1d_nolp_misalign_op.register_fake
 def _(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode):
     return torch.empty_like(rewards), torch.empty_like(rewards)
+
+
+def gae_1d_nolp_misalign(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode):
+    if _eager():
+        return _raw_gae_1d_nolp_misalign(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode)
+    return gae_1d_nolp_misalign_op(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode)
 
 
 # --------------------------------------------------------------------------------------------
 # H2 PPO loss
 # --------------------------------------------------------------------------------------------
-@torch.library.custom_op("b200rl::ppo_loss_fwd", mutates_args=())
-def ppo_loss_fwd(
+def _raw_ppo_loss_fwd(
     logp: Tensor, prox_logp: Tensor, old_logp: Tensor, adv: Tensor, mask: Tensor,
     clip_lo: float, clip_hi: float, c_clip: float, cap: float,
     adv_mean: Optional[Tensor], adv_denom: Optional[Tensor], adv_group: Optional[Tensor],
@@ -215,7 +291,7 @@ def ppo_loss_fwd(
         if adv_group.numel() != T:
             raise RuntimeError("adv_group must have one entry per token")
     ws = _lib.workspace(lib.b200rl_ppo_loss_workspace_bytes(T), dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_ppo_loss_fwd(
             ptr(lp), ptr(px), ptr(ol), ptr(ad), ptr(mk), T, float(clip_lo), float(clip_hi),
             float(c_clip), float(cap), ptr(adv_mean), ptr(adv_denom), ptr(adv_group),
@@ -229,7 +305,10 @@ def ppo_loss_fwd(
             rs(s_kl), rs(s_clip), rs(s_dual), rs(s_bw), rs(s_bkl), rs(s_bm)]
 
 
-@ppo_loss_fwd.register_fake
+ppo_loss_fwd_op = torch.library.custom_op("b200rl::ppo_loss_fwd", _raw_ppo_loss_fwd, mutates_args=())
+
+
+@ppo_loss_fwd_op.register_fake
 def _(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap, adv_mean, adv_denom, adv_group):
     f = lambda: torch.empty_like(logp, dtype=torch.float32)
     b = lambda: torch.empty_like(logp, dtype=torch.uint8)
@@ -239,20 +318,22 @@ def _(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap, adv_m
             f(), f(), b()]
 
 
-@torch.library.custom_op("b200rl::ppo_loss_bwd", mutates_args=())
-def ppo_loss_bwd(dlogp: Tensor, grad_loss: Tensor, denom: Tensor) -> Tensor:
+def _raw_ppo_loss_bwd(dlogp: Tensor, grad_loss: Tensor, denom: Tensor) -> Tensor:
     _lib.require_cuda(dlogp=dlogp, grad_loss=grad_loss, denom=denom)
     dev = dlogp.device
     d = dlogp.contiguous()
     g = torch.empty_like(d)
     gl = grad_loss.to(torch.float32).reshape(1).contiguous()
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_ppo_loss_bwd(ptr(d), ptr(gl), ptr(denom), ptr(g), d.numel(), stream_handle(dev))
     check(rc, "b200rl_ppo_loss_bwd")
     return g
 
 
-@ppo_loss_bwd.register_fake
+ppo_loss_bwd_op = torch.library.custom_op("b200rl::ppo_loss_bwd", _raw_ppo_loss_bwd, mutates_args=())
+
+
+@ppo_loss_bwd_op.register_fake
 def _(dlogp, grad_loss, denom):
     return torch.empty_like(dlogp)
 
@@ -266,19 +347,51 @@ def _loss_backward(ctx, grads):
     g_loss = grads[0]
     g_lp = None
     if g_loss is not None:
-        g_lp = ppo_loss_bwd(dlogp, g_loss, denom)
+        g_lp = ppo_loss_bwd_op(dlogp, g_loss, denom)
     # like the reference in practice: only `logprobs` carries a gradient
     return (g_lp,) + (None,) * 11
 
 
-ppo_loss_fwd.register_autograd(_loss_backward, setup_context=_loss_setup_context)
+ppo_loss_fwd_op.register_autograd(_loss_backward, setup_context=_loss_setup_context)
+
+
+class _PpoLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap,
+                adv_mean, adv_denom, adv_group):
+        out = _raw_ppo_loss_fwd(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap,
+                                adv_mean, adv_denom, adv_group)
+        ctx.save_for_backward(out[2], out[1])
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(*out[1:])
+        return tuple(out)
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        dlogp, denom = ctx.saved_tensors
+        g_lp = None if g_loss is None else _raw_ppo_loss_bwd(dlogp, g_loss, denom)
+        return (g_lp,) + (None,) * 11
+
+
+def ppo_loss_fwd(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap,
+                 adv_mean, adv_denom, adv_group):
+    args = (logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap, adv_mean, adv_denom,
+            adv_group)
+    if not _eager():
+        return ppo_loss_fwd_op(*args)
+    if logp.requires_grad and torch.is_grad_enabled():
+        return list(_PpoLossFn.apply(*args))
+    return _raw_ppo_loss_fwd(*args)
+
+
+def ppo_loss_bwd(dlogp, grad_loss, denom):
+    return _raw_ppo_loss_bwd(dlogp, grad_loss, denom) if _eager() else ppo_loss_bwd_op(dlogp, grad_loss, denom)
 
 
 # --------------------------------------------------------------------------------------------
 # H2 masked moments / normalisation
 # --------------------------------------------------------------------------------------------
-@torch.library.custom_op("b200rl::masked_moments", mutates_args=())
-def masked_moments(
+def _raw_masked_moments(
     x: Tensor, mask: Optional[Tensor], group_elems: int, center: Optional[Tensor],
     center_group_elems: int,
 ) -> Tensor:
@@ -292,7 +405,7 @@ def masked_moments(
     if n == 0:
         return mom
     ws = _lib.workspace(lib.b200rl_moments_workspace_bytes(n, group_elems), dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_masked_moments(
             ptr(x), ptr(mask), n, group_elems, ptr(center), center_group_elems, ptr(mom),
             ptr(ws), ws.numel(), stream_handle(dev),
@@ -301,13 +414,21 @@ def masked_moments(
     return mom
 
 
-@masked_moments.register_fake
+masked_moments_op = torch.library.custom_op("b200rl::masked_moments", _raw_masked_moments, mutates_args=())
+
+
+@masked_moments_op.register_fake
 def _(x, mask, group_elems, center, center_group_elems):
     return x.new_empty((x.numel() // group_elems, 3), dtype=torch.float64)
 
 
-@torch.library.custom_op("b200rl::moments_finalize", mutates_args=())
-def moments_finalize(moments: Tensor, centered: bool, unbiased: bool, eps: float) -> Tuple[Tensor, Tensor]:
+def masked_moments(x, mask, group_elems, center, center_group_elems):
+    if _eager():
+        return _raw_masked_moments(x, mask, group_elems, center, center_group_elems)
+    return masked_moments_op(x, mask, group_elems, center, center_group_elems)
+
+
+def _raw_moments_finalize(moments: Tensor, centered: bool, unbiased: bool, eps: float) -> Tuple[Tensor, Tensor]:
     """-> (mean[G], denom[G] = sqrt(var) + eps), fp64."""
     _lib.require_cuda(moments=moments)
     _lib.require_contiguous(moments=moments)
@@ -315,21 +436,29 @@ def moments_finalize(moments: Tensor, centered: bool, unbiased: bool, eps: float
     dev = moments.device
     mean = torch.empty(G, dtype=torch.float64, device=dev)
     denom = torch.empty(G, dtype=torch.float64, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_moments_finalize(ptr(moments), G, int(centered), int(unbiased), float(eps),
                                          ptr(mean), ptr(denom), stream_handle(dev))
     check(rc, "b200rl_moments_finalize")
     return mean, denom
 
 
-@moments_finalize.register_fake
+moments_finalize_op = torch.library.custom_op("b200rl::moments_finalize", _raw_moments_finalize, mutates_args=())
+
+
+@moments_finalize_op.register_fake
 def _(moments, centered, unbiased, eps):
     G = moments.shape[0]
     return moments.new_empty((G,)), moments.new_empty((G,))
 
 
-@torch.library.custom_op("b200rl::masked_normalize", mutates_args=())
-def masked_normalize(
+def moments_finalize(moments, centered, unbiased, eps):
+    if _eager():
+        return _raw_moments_finalize(moments, centered, unbiased, eps)
+    return moments_finalize_op(moments, centered, unbiased, eps)
+
+
+def _raw_masked_normalize(
     x: Tensor, mask: Optional[Tensor], mean: Optional[Tensor], mean_group_elems: int,
     denom: Optional[Tensor], denom_group_elems: int, mask_x: bool,
 ) -> Tensor:
@@ -337,7 +466,7 @@ def masked_normalize(
     _lib.require_contiguous(x=x, mask=mask, mean=mean, denom=denom)
     out = torch.empty_like(x, dtype=torch.float32)
     dev = x.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_masked_normalize(
             ptr(x), ptr(mask), x.numel(), ptr(mean), mean_group_elems, ptr(denom),
             denom_group_elems, int(mask_x), ptr(out), stream_handle(dev),
@@ -346,9 +475,18 @@ def masked_normalize(
     return out
 
 
-@masked_normalize.register_fake
+masked_normalize_op = torch.library.custom_op("b200rl::masked_normalize", _raw_masked_normalize, mutates_args=())
+
+
+@masked_normalize_op.register_fake
 def _(x, mask, mean, mean_group_elems, denom, denom_group_elems, mask_x):
     return torch.empty_like(x, dtype=torch.float32)
+
+
+def masked_normalize(x, mask, mean, mean_group_elems, denom, denom_group_elems, mask_x):
+    if _eager():
+        return _raw_masked_normalize(x, mask, mean, mean_group_elems, denom, denom_group_elems, mask_x)
+    return masked_normalize_op(x, mask, mean, mean_group_elems, denom, denom_group_elems, mask_x)
 
 
 # --------------------------------------------------------------------------------------------
@@ -375,7 +513,7 @@ def slice_intervals_op(
     n = _check_intervals(intervals)
     dev = src.device
     dst = torch.empty((total_size,), dtype=src.dtype, device=dev)  # interval_op.cu:82
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_slice_intervals(
             ptr(src), src.numel(), ptr(dst), total_size, ptr(intervals), n, src.element_size(),
             ptr(workspace), workspace.numel(), int(reuse_plan), stream_handle(dev),
@@ -399,7 +537,7 @@ def set_intervals_op(
         raise RuntimeError("Source and destination tensors must have the same dtype")
     n = _check_intervals(intervals)
     dev = src.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = lib.b200rl_set_intervals(
             ptr(src), src.numel(), ptr(dst), dst.numel(), ptr(intervals), n, src.element_size(),
             ptr(workspace), workspace.numel(), int(reuse_plan), stream_handle(dev),

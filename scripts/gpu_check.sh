@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,memory.total,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
 echo "== smoke" ; timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"
 tail -3 gpurun_out/smoke.log
-for f in tests/test_*_gpu.py; do
+for f in tests/test_*_gpu.py tests/test_zz_no_alloc.py; do
   n=$(basename $f .py)
   timeout 900 python -m pytest $f -q -m gpu --maxfail=25 -p no:cacheprovider > gpurun_out/$n.log 2>&1
   echo "== $n rc=$?"; tail -4 gpurun_out/$n.log

@@ -1,10 +1,10 @@
 #!/bin/bash
 mkdir -p gpurun_out
 python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > gpurun_out/plain_bench.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > gpurun_out/ncu_bench.log 2>&1
 echo "launch list rc=$?"
 python scripts/prof_h1.py 2048 h1 > gpurun_out/plain_h1.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:logprob_ -s 4 -c 4 -o gpurun_out/prof_h1 \
     python scripts/prof_h1.py 2048 h1 > gpurun_out/ncu_h1.log 2>&1
-echo "full rc=$?"; tail -3 gpurun_out/ncu_h1.log
+echo "full rc=$?"; tail -2 gpurun_out/ncu_h1.log
