@@ -135,7 +135,6 @@ constexpr int kMetaCnt = (1 << 24) - 1;
 
 struct ScanSmem {
   float d[kTile];    // delta, then adv (zero carry-in)
-  float v[kTile];    // value of the token
   int meta[kTile];   // start-count / relative sequence id, LAST/BOOT flags
 };
 
@@ -174,7 +173,7 @@ __device__ __forceinline__ int count_ends_le(const int32_t* __restrict__ cu, int
   return lo - 1;
 }
 
-__global__ void __launch_bounds__(kScanWarps * 32)
+__global__ void __launch_bounds__(kScanWarps * 32, 6)
 gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
                 const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot,
                 float* __restrict__ adv, float* __restrict__ ret, int batch, int total,
@@ -189,6 +188,8 @@ gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ val
   (void)c4;
 
   while (true) {
+    // a ticket is taken only when the warp is ready to work on it: a tile that looks back at its
+    // right neighbour then finds that neighbour already in progress, not queued behind other work
     unsigned int ticket = 0;
     if (lane == 0) ticket = atomicAdd(ticket_ctr, 1u);
     ticket = __shfl_sync(0xffffffffu, ticket, 0);
@@ -265,7 +266,6 @@ gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ val
         float nv = nn[j];
         if ((mm[j] & kMetaLast) && !(mm[j] & kMetaBoot)) nv = 0.f;
         S.d[o] = (o < tlen) ? fmaf(gamma, nv, rr[j]) - vv[j] : 0.f;
-        S.v[o] = vv[j];
         if (o >= tlen) S.meta[o] = 0;
       }
     }
@@ -353,14 +353,26 @@ gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ val
     }
 
     // ---- write back (coalesced); tokens right of the last boundary take the carry -----------
-#pragma unroll 2
-    for (int k = 0; k < kTile / 32; k++) {
-      const int o = k * 32 + lane;
-      if (o < tlen) {
-        float A = S.d[o];
-        if (need_carry && o > last_boundary) A = fmaf(exp2f(lc * (float)(tlen - o)), Xin, A);
-        adv[tlo + o] = A;
-        ret[tlo + o] = A + S.v[o];
+    // v is read again for ret = adv + v: the tile was streamed microseconds ago, so this is an
+    // L2 hit, and not keeping it in shared memory buys 50% more resident warps.
+#pragma unroll 1
+    for (int kb = 0; kb < kTile / 32; kb += 8) {
+      float vv[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const int o = (kb + j) * 32 + lane;
+        const int64_t vi = (int64_t)tlo + o + i_lo + (S.meta[o] & kMetaCnt);
+        vv[j] = (o < tlen) ? values[vi] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const int o = (kb + j) * 32 + lane;
+        if (o < tlen) {
+          float A = S.d[o];
+          if (need_carry && o > last_boundary) A = fmaf(ex2_approx(lc * (float)(tlen - o)), Xin, A);
+          adv[tlo + o] = A;
+          ret[tlo + o] = A + vv[j];
+        }
       }
     }
     __syncwarp();
@@ -438,7 +450,7 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
       attr_set[dev] = true;
     }
     int grid = (W.num_tiles + kScanWarps - 1) / kScanWarps;
-    const int cap = sm_count() * 4;  // 4 CTAs x 4 warps x 12 KiB = 192 KiB smem per SM
+    const int cap = sm_count() * 6;  // 6 CTAs x 4 warps x 8 KiB = 192 KiB smem per SM
     if (grid > cap) grid = cap;
     gae_scan_kernel<<<grid, kScanWarps * 32, smem, st>>>(rewards, values, cu_seqlens, bootstrap,
                                                         adv, ret, batch, (int)total, gamma, lam,
@@ -522,7 +534,7 @@ extern "C" int b200rl_gae_1d_nolp_misalign_noalloc(const float* rewards, const f
   // the array keeps whatever the previous call left: ticket counter and tile states must be zero
   B200RL_CUDA(cudaMemsetAsync(scratch, 0, W.bytes, st));
   int grid = (W.num_tiles + kScanWarps - 1) / kScanWarps;
-  const int cap = sm_count() * 4;
+  const int cap = sm_count() * 6;
   if (grid > cap) grid = cap;
   gae_scan_kernel<<<grid, kScanWarps * 32, sizeof(ScanSmem) * kScanWarps, st>>>(
       rewards, values, cu_seqlens, bootstrap, adv, ret, batch, (int)total, gamma, lam, W.state,

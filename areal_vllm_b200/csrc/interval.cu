@@ -229,11 +229,75 @@ __device__ __forceinline__ void copy_piece_w(const char* s, char* d, int64_t byt
   }
 }
 
+
+// Mutually misaligned piece ((s - d) % 16 != 0) moved with 16-byte accesses on BOTH sides: stores
+// are aligned on d; every lane loads the aligned source vector under its store, takes the next one
+// from its neighbour lane by shuffle, and funnel-shifts the 32-byte window by the (warp-uniform)
+// byte phase. Reads stay inside [floor16(s'), s' + body + 16), i.e. inside the interval except for
+// < 16 bytes before it, which is still inside the (16-byte aligned) source allocation.
+template <int K>
+__device__ __forceinline__ uint4 shift_window(const uint4& lo, const uint4& hi, unsigned bits) {
+  const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+  uint4 o;
+  o.x = __funnelshift_r(w[K + 0], w[K + 1], bits);
+  o.y = __funnelshift_r(w[K + 1], w[K + 2], bits);
+  o.z = __funnelshift_r(w[K + 2], w[K + 3], bits);
+  o.w = __funnelshift_r(w[K + 3], w[K + 4], bits);
+  return o;
+}
+
 template <int ES>
-__device__ __forceinline__ void copy_piece(const char* s, char* d, int64_t bytes, int lane) {
+__device__ __forceinline__ void copy_piece_shift(const char* s, char* d, int64_t bytes, int lane) {
+  int head = (int)((16 - (reinterpret_cast<uintptr_t>(d) & 15)) & 15);
+  if (head > bytes) head = (int)bytes;
+  copy_small<ES>(s, d, head, lane);
+  s += head;
+  d += head;
+  bytes -= head;
+  const unsigned ph = (unsigned)(reinterpret_cast<uintptr_t>(s) & 15);  // 1..15, warp-uniform
+  const char* a = s - ph;                                               // 16-B aligned
+  const int64_t nv = bytes >= 32 ? (bytes - 16) / 16 : 0;               // keep the over-read inside
+  const unsigned k = ph >> 2, bits = (ph & 3) * 8;
+  constexpr int U = 4;
+  for (int64_t v0 = 0; v0 < nv; v0 += 32 * U) {
+    uint4 lo[U], ex[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t v = v0 + 32 * u + lane;
+      lo[u] = make_uint4(0, 0, 0, 0);
+      ex[u] = make_uint4(0, 0, 0, 0);
+      if (v <= nv) lo[u] = ldg_nc_v4(a + v * 16);  // vector nv is the last window's upper half
+      if (lane == 31 && v < nv) ex[u] = ldg_nc_v4(a + (v + 1) * 16);  // neighbour of the last lane
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t v = v0 + 32 * u + lane;
+      uint4 hi;
+      hi.x = __shfl_down_sync(0xffffffffu, lo[u].x, 1);
+      hi.y = __shfl_down_sync(0xffffffffu, lo[u].y, 1);
+      hi.z = __shfl_down_sync(0xffffffffu, lo[u].z, 1);
+      hi.w = __shfl_down_sync(0xffffffffu, lo[u].w, 1);
+      if (lane == 31) hi = ex[u];
+      uint4 o;
+      switch (k) {
+        case 0: o = shift_window<0>(lo[u], hi, bits); break;
+        case 1: o = shift_window<1>(lo[u], hi, bits); break;
+        case 2: o = shift_window<2>(lo[u], hi, bits); break;
+        default: o = shift_window<3>(lo[u], hi, bits); break;
+      }
+      if (v < nv) stg_na_v4(d + v * 16, o);
+    }
+  }
+  copy_small<ES>(s + nv * 16, d + nv * 16, (int)(bytes - nv * 16), lane);
+}
+
+template <int ES>
+__device__ __forceinline__ void copy_piece(const char* s, char* d, int64_t bytes, int lane, bool src_base_aligned) {
   const unsigned rel = (unsigned)((reinterpret_cast<uintptr_t>(s) - reinterpret_cast<uintptr_t>(d)) & 15u);
   if (rel == 0) {
     copy_piece_w<16, ES>(s, d, bytes, lane);
+  } else if (src_base_aligned && bytes >= 4096) {
+    copy_piece_shift<ES>(s, d, bytes, lane);
   } else if constexpr (ES < 8) {
     if ((rel & 7u) == 0) {
       copy_piece_w<8, ES>(s, d, bytes, lane);
@@ -256,7 +320,7 @@ __device__ __forceinline__ void copy_piece(const char* s, char* d, int64_t bytes
 
 // MODE 0: slice (big -> packed).  MODE 1: set (packed -> big).
 template <int MODE, int ES>
-__global__ void __launch_bounds__(kCopyWarps * 32)
+__global__ void __launch_bounds__(kCopyWarps * 32, 4)
 interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
                      const int64_t* __restrict__ intervals, const int64_t* __restrict__ offsets,
                      const int32_t* __restrict__ tile_first, const int64_t* __restrict__ hdr,
@@ -264,6 +328,7 @@ interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
   const int lane = threadIdx.x & 31;
   const int64_t tile = (int64_t)blockIdx.x * kCopyWarps + (threadIdx.x >> 5);
   if (tile >= num_tiles) return;
+  const bool src_ok = (reinterpret_cast<uintptr_t>(src) & 15) == 0;  // allows aligned over-reads
   int64_t total_elems = hdr[0];
   if (total_elems > hdr[3]) total_elems = hdr[3];  // never write past the packed buffer
   const int64_t total_bytes = total_elems * ES;
@@ -281,8 +346,8 @@ interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
     const int64_t start = intervals[2 * i] * ES;
     const int64_t b = oe < p1 ? oe : p1;
     const int64_t big_off = start + (p0 - ob);
-    if (MODE == 0) copy_piece<ES>(src + big_off, dst + p0, b - p0, lane);
-    else           copy_piece<ES>(src + p0, dst + big_off, b - p0, lane);
+    if (MODE == 0) copy_piece<ES>(src + big_off, dst + p0, b - p0, lane, src_ok);
+    else           copy_piece<ES>(src + p0, dst + big_off, b - p0, lane, src_ok);
     p0 = b;
     if (b == oe) i++;
   }

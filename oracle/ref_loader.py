@@ -108,3 +108,26 @@ def merge_intervals_ext():
             spec.loader.exec_module(mod)
             return mod.merge_intervals
     return None
+
+
+def _load_ref_so(name: str):
+    """A pybind module compiled by oracle/build_ref_cuda.py from the reference's own .cu file."""
+    import torch  # noqa: F401  (the extension links against libtorch)
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", name + ".so")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def ref_cugae_cuda():
+    """csrc/cugae/gae.cu compiled for sm_100a (gae_1d_nolp_misalign, gae_2d_olp, gae_2d_nolp)."""
+    return _load_ref_so("ref_cugae")
+
+
+def ref_interval_op_cuda():
+    """csrc/interval_op/interval_op.cu compiled for sm_100a (slice/set_intervals_{fp32,fp16,bf16})."""
+    return _load_ref_so("ref_interval_op_cuda")

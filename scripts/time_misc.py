@@ -43,6 +43,24 @@ def gae_case(name, B, lo, hi, seed):
         gbs = 16.0 * total / ms / 1e6
         print(f"GAE {name:22s} {mname:6s} B={B:6d} tokens={total:9d}  {ms*1e3:9.1f} us  {total/ms/1e6:9.2f} Gtok/s  {gbs:7.0f} GB/s ({gbs/PEAK:5.3f})")
 
+from oracle import ref_loader as R
+REF_GAE, REF_IV = R.ref_cugae_cuda(), R.ref_interval_op_cuda()
+
+def ref_gae_case(name, B, lo, hi, seed):
+    if REF_GAE is None:
+        return
+    rng = np.random.default_rng(seed)
+    lens = rng.integers(lo, hi + 1, B)
+    total = int(lens.sum())
+    r = torch.randn(total, device=dev); v = torch.randn(total + B, device=dev)
+    cu = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)).to(dev)
+    b = torch.ones(B, dtype=torch.bool, device=dev)
+    ms = timeit(lambda: REF_GAE.gae_1d_nolp_misalign(r, v, cu, b, 0.99, 0.95), iters=8)
+    print(f"GAE {name:22s} REFERENCE gae.cu (sm_100a build)      {ms*1e3:9.1f} us  {total/ms/1e6:9.2f} Gtok/s")
+
+for args in (("cfg1 256x[64,2048]", 256, 64, 2048, 1), ("cfg4 120x[1k,16k]", 120, 1024, 16384, 4),
+             ("large 65536x[64,2048]", 65536, 64, 2048, 2)):
+    ref_gae_case(*args)
 gae_case("cfg1 256x[64,2048]", 256, 64, 2048, 1)
 gae_case("cfg4 120x[1k,16k]", 120, 1024, 16384, 4)
 gae_case("large 65536x[64,2048]", 65536, 64, 2048, 2)
@@ -67,6 +85,11 @@ def interval_case(name, size, iv, dtype=torch.bfloat16):
         pkg.flatten_param.slice_intervals(src, intervals_cuda=ivc, output_size=total)
     ms_p = timeit(replan, iters=5)
     gb = 2.0 * total * es / 1e9
+    if REF_IV is not None and dtype == torch.bfloat16:
+        mx = int((iv[:, 1] - iv[:, 0]).max())
+        ms_r = timeit(lambda: REF_IV.slice_intervals_bf16(src, ivc, total, mx), iters=3, warm=1)
+        ms_rs = timeit(lambda: REF_IV.set_intervals_bf16(out, dst, ivc, mx), iters=3, warm=1)
+        print(f"INTERVAL {name:34s} REFERENCE interval_op.cu: slice {ms_r*1e3:9.1f} us {gb/ms_r*1e3:7.0f} GB/s  set {ms_rs*1e3:9.1f} us {gb/ms_rs*1e3:7.0f} GB/s")
     print(f"INTERVAL {name:34s} N={len(iv):7d} copied={total*es/1e9:7.3f} GB  slice {ms_s*1e3:9.1f} us {gb/ms_s*1e3:7.0f} GB/s ({gb/ms_s*1e3/PEAK:5.3f})"
           f"  set {ms_t*1e3:9.1f} us {gb/ms_t*1e3:7.0f} GB/s ({gb/ms_t*1e3/PEAK:5.3f})  slice+plan {ms_p*1e3:9.1f} us")
     del src, dst, out
