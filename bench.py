@@ -223,6 +223,77 @@ def main_reference(args):
     print(json.dumps(out), flush=True)
 
 
+
+# ------------------------------------------------------------------------------------------
+# secondary metrics of the same path (BASELINE.json: "GAE tokens/s", interval_op GB/s)
+# ------------------------------------------------------------------------------------------
+def run_extras(dev, peak):
+    import areal_vllm_b200 as pkg
+    from areal_vllm_b200 import _lib
+    from oracle import cpu_ref
+
+    flush = torch.empty(256 * 2**20, dtype=torch.uint8, device=dev)
+
+    def timeit(fn, iters=10, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(iters):
+            flush.zero_()  # L2 flush between timed iterations (inputs below can be < L2)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        return float(np.median(ts))
+
+    out = {"gae": [], "interval_op": []}
+    for name, B, lo, hi, seed in (("cfg1: 256 seqs, len 64-2048", 256, 64, 2048, 1),
+                                  ("cfg1 length law x256: 65536 seqs", 65536, 64, 2048, 2)):
+        rng = np.random.default_rng(seed)
+        lens = rng.integers(lo, hi + 1, B)
+        total = int(lens.sum())
+        r_np = rng.standard_normal(total).astype(np.float32)
+        v_np = rng.standard_normal(total + B).astype(np.float32)
+        cu_np = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+        r, v, cu = (torch.from_numpy(a).to(dev) for a in (r_np, v_np, cu_np))
+        b = torch.ones(B, dtype=torch.bool, device=dev)
+        for gamma, lam in ((0.99, 0.95), (1.0, 1.0)):
+            ms = timeit(lambda: pkg.ppo_functional.cugae1d_nolp_misalign_func(r, v, cu, b, gamma, lam))
+            rec = {"workload": name, "gamma": gamma, "lam": lam, "tokens": total,
+                   "kernel": "gae_scan_kernel" if gamma * lam <= 0.99 else "gae_serial_kernel",
+                   "us": ms * 1e3, "tokens_per_s": total / (ms * 1e-3),
+                   "hbm_frac_of_measured_peak": 16.0 * total / (ms * 1e-3) / 1e9 / peak}
+            if B == 256:  # CPU baseline: C port of pygae1d_nolp_misalign, one thread (the python
+                t0 = time.perf_counter()  # reference is a scalar loop and cannot use more)
+                cpu_ref.gae_py(r_np, v_np, cu_np, np.ones(B, np.float32), gamma, lam)
+                rec["cpu_port_tokens_per_s"] = total / (time.perf_counter() - t0)
+            out["gae"].append(rec)
+    # interval_op, BASELINE config 5: 7B bf16 flat buffer, 1e5 intervals (reference test's generator)
+    size, n = 7_615_616_512, 100000
+    free, _ = torch.cuda.mem_get_info()
+    if free > 26 * 2**30:
+        s_ = size // n
+        iv = np.array([(i * s_, i * s_ + s_ // 2) for i in range(n)], dtype=np.int64)
+        np.random.default_rng(5).shuffle(iv)
+        src = torch.empty(size, dtype=torch.bfloat16, device=dev)
+        src.view(torch.int16).random_()
+        ivc = torch.from_numpy(iv).to(dev)
+        total = int((iv[:, 1] - iv[:, 0]).sum())
+        packed = pkg.flatten_param.slice_intervals(src, intervals_cuda=ivc, output_size=total)
+        ms_s = timeit(lambda: pkg.flatten_param.slice_intervals(src, intervals_cuda=ivc, output_size=total), iters=5)
+        ms_t = timeit(lambda: pkg.flatten_param.set_intervals(packed, src, intervals_cuda=ivc), iters=5)
+        gb = 4.0 * total / 1e9
+        out["interval_op"].append({
+            "workload": "cfg5: 7,615,616,512-element bf16 buffer, 1e5 shuffled intervals (half the buffer)",
+            "copied_GB": 2.0 * total / 1e9, "slice_us": ms_s * 1e3, "slice_GBps": gb / (ms_s * 1e-3),
+            "slice_frac_of_measured_peak": gb / (ms_s * 1e-3) / peak, "set_us": ms_t * 1e3,
+            "set_GBps": gb / (ms_t * 1e-3), "set_frac_of_measured_peak": gb / (ms_t * 1e-3) / peak})
+        del src, packed
+    return out
+
 # ------------------------------------------------------------------------------------------
 # the b200rl arm
 # ------------------------------------------------------------------------------------------
@@ -349,11 +420,18 @@ def main_b200rl(args):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):  # dram__bytes_read+write per [T,V] row from the last ncu --set full capture
+        per_row = json.load(open(tpath)).get("logprob_bwd_bf16_kernel_bytes_per_row")
+        if per_row:
+            traffic = per_row * (sum(T for _, _, T in bwd_events) / max(len(bwd_events), 1))
     achieved = bwd_bytes / (bwd_ms * 1e-3) / 1e9
     roofline = {
         "kernel": "logprob_bwd_bf16_kernel (+ppo_loss_bwd_kernel, <0.1%)", "bound": "hbm",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None, "peak_source": peak_src,
+        "traffic": traffic, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": bwd_bytes / max(len(bwd_events), 1),
         "algorithmic_bytes_per_token": 4 * V, "launches_timed": len(bwd_events),
         "fwd": {"kernel": "logprob_fwd_bf16_kernel<ENT,MINMAX> (+ppo_loss_fwd, stats)",
                 "achieved": fwd_bytes / (fwd_ms * 1e-3) / 1e9,
@@ -438,6 +516,11 @@ def main_b200rl(args):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu_baseline = run_cpu_baseline()
+    extras = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        del logits_bufs[:]
+        torch.cuda.empty_cache()
+        extras = run_extras(dev, peak)
 
     if rank == 0:
         n_mb = len(mbs)
@@ -451,6 +534,7 @@ def main_b200rl(args):
                        "cache": f"inputs larger than L2: {N_LOGITS_BUFFERS} rotating logits buffers of "
                                 f"{max_T}x{V} bf16 = {max_T * V * 2 / 1e9:.2f} GB each"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "clocks": clocks,
+            "extra": extras,
             "gpu_launches": args.steps * (3 + 4 * n_mb),
             "gpu_launches_note": "per step: masked_moments+moments_finalize+masked_normalize, then per "
                                  "micro-batch logprob_fwd, ppo_loss_fwd, ppo_loss_bwd, logprob_bwd",
@@ -463,11 +547,12 @@ def main_b200rl(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200rl", choices=["b200rl", "reference"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the GAE / interval_op side metrics")
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)

@@ -1,8 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > gpurun_out/plain_bench.log 2>&1 && \
+python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu --no-extras > gpurun_out/plain_bench.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
-    python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu > gpurun_out/ncu_bench.log 2>&1
+    python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu --no-extras > gpurun_out/ncu_bench.log 2>&1
 echo "launch list rc=$?"
 python scripts/prof_h1.py 2048 h1 > gpurun_out/plain_h1.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:logprob_ -s 4 -c 4 -o gpurun_out/prof_h1 \

@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_logprob_gpu.py tests/test_loss_advnorm_gpu.py -q -m gpu -x -p no:cacheprovider > gpurun_out/quick_tests.log 2>&1
 echo "tests rc=$?"; tail -3 gpurun_out/quick_tests.log
 timeout 300 python scripts/time_h1.py > gpurun_out/time_h1.log 2>&1; echo "time rc=$?"; cat gpurun_out/time_h1.log | tail -12
-timeout 600 python bench.py --steps 5 --warmup 2 --no-e2e --no-cpu > gpurun_out/bench_quick.log 2>gpurun_out/bench_quick.err; echo "bench rc=$?"
+timeout 600 python bench.py --steps 5 --warmup 2 --no-e2e --no-cpu --no-extras > gpurun_out/bench_quick.log 2>gpurun_out/bench_quick.err; echo "bench rc=$?"
 python - <<'PY'
 import json
 try:
