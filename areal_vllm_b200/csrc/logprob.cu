@@ -17,7 +17,8 @@
 //            softmax is never materialised.
 //
 // Bound: HBM. Algorithmic bytes per token: fwd 2*V, bwd 4*V (bf16 logits).
-// fp16/fp32 logits and vocabularies whose rows are not 16-byte aligned take a plain
+// The same kernels are instantiated for fp16 and fp32 logits (fp32: 4 elements per 16-byte vector,
+// 4*V / 8*V bytes per token). Vocabularies whose rows are not 16-byte aligned take a plain
 // (non-TMA) kernel further down: correct, not tuned.
 #include "common.cuh"
 
@@ -28,9 +29,121 @@ constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThr = 8.0f;       // log2 units a new element may exceed the lane's reference
 constexpr float kSentinel = 1.0e30f;      // -reference of a lane that has seen nothing yet
-constexpr uint32_t kNeutral = 0xF14AF14Au;  // bf16 pair ~ -1e30: exp -> 0, finite products
 constexpr uint32_t kNegInf2 = 0xFF80FF80u;
 constexpr uint32_t kPosInf2 = 0x7F807F80u;
+
+
+// Element traits of the three logits dtypes. A 16-byte vector holds kPerVec elements on the way
+// in (logits) and on the way out (dlogits), so vector indices coincide for every dtype.
+template <int DT> struct Elem;
+
+template <> struct Elem<B200RL_BF16> {
+  static constexpr int kPerVec = 8, kBytes = 2;
+  static constexpr uint32_t kNeutralWord = 0xF14AF14Au;  // pair of ~-1e30: exp -> 0, finite products
+  using MaxT = uint32_t;  // packed bf16x2 running extremum
+  static __device__ __forceinline__ MaxT max_init() { return kNegInf2; }
+  static __device__ __forceinline__ MaxT min_init() { return kPosInf2; }
+  static __device__ __forceinline__ MaxT cmax(MaxT a, MaxT b) { return max_bf16x2(a, b); }
+  static __device__ __forceinline__ MaxT cmin(MaxT a, MaxT b) { return min_bf16x2(a, b); }
+  static __device__ __forceinline__ MaxT vmax(const uint4& v) { return cmax(cmax(v.x, v.y), cmax(v.z, v.w)); }
+  static __device__ __forceinline__ MaxT vmin(const uint4& v) { return cmin(cmin(v.x, v.y), cmin(v.z, v.w)); }
+  static __device__ __forceinline__ float max_f(MaxT m) { return fmaxf(bf16lo(m), bf16hi(m)); }
+  static __device__ __forceinline__ float min_f(MaxT m) { return fminf(bf16lo(m), bf16hi(m)); }
+  static __device__ __forceinline__ void unpack(const uint4& v, float (&x)[8]) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      x[2 * j] = bf16lo(w[j]);
+      x[2 * j + 1] = bf16hi(w[j]);
+    }
+  }
+  static __device__ __forceinline__ uint4 pack(const float (&d)[8]) {
+    return make_uint4(pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]),
+                      pack_bf16x2(d[6], d[7]));
+  }
+  static __device__ __forceinline__ float load1(const void* base, int64_t i) {
+    return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[i]);
+  }
+};
+
+template <> struct Elem<B200RL_FP16> {
+  static constexpr int kPerVec = 8, kBytes = 2;
+  static constexpr uint32_t kNeutralWord = 0xFBFFFBFFu;  // pair of -65504 (largest finite |fp16|)
+  using MaxT = uint32_t;  // packed f16x2
+  static __device__ __forceinline__ MaxT max_init() { return 0xFC00FC00u; }
+  static __device__ __forceinline__ MaxT min_init() { return 0x7C007C00u; }
+  static __device__ __forceinline__ MaxT cmax(MaxT a, MaxT b) {
+    uint32_t r;
+    asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+  }
+  static __device__ __forceinline__ MaxT cmin(MaxT a, MaxT b) {
+    uint32_t r;
+    asm("min.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+  }
+  static __device__ __forceinline__ MaxT vmax(const uint4& v) { return cmax(cmax(v.x, v.y), cmax(v.z, v.w)); }
+  static __device__ __forceinline__ MaxT vmin(const uint4& v) { return cmin(cmin(v.x, v.y), cmin(v.z, v.w)); }
+  static __device__ __forceinline__ float2 f2(uint32_t w) {
+    return __half22float2(*reinterpret_cast<const __half2*>(&w));
+  }
+  static __device__ __forceinline__ float max_f(MaxT m) { float2 f = f2(m); return fmaxf(f.x, f.y); }
+  static __device__ __forceinline__ float min_f(MaxT m) { float2 f = f2(m); return fminf(f.x, f.y); }
+  static __device__ __forceinline__ void unpack(const uint4& v, float (&x)[8]) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const float2 f = f2(w[j]);
+      x[2 * j] = f.x;
+      x[2 * j + 1] = f.y;
+    }
+  }
+  static __device__ __forceinline__ uint4 pack(const float (&d)[8]) {
+    uint4 o;
+    __half2 h;
+    h = __floats2half2_rn(d[0], d[1]); o.x = *reinterpret_cast<uint32_t*>(&h);
+    h = __floats2half2_rn(d[2], d[3]); o.y = *reinterpret_cast<uint32_t*>(&h);
+    h = __floats2half2_rn(d[4], d[5]); o.z = *reinterpret_cast<uint32_t*>(&h);
+    h = __floats2half2_rn(d[6], d[7]); o.w = *reinterpret_cast<uint32_t*>(&h);
+    return o;
+  }
+  static __device__ __forceinline__ float load1(const void* base, int64_t i) {
+    return __half2float(reinterpret_cast<const __half*>(base)[i]);
+  }
+};
+
+template <> struct Elem<B200RL_FP32> {
+  static constexpr int kPerVec = 4, kBytes = 4;
+  static constexpr uint32_t kNeutralWord = 0xF149F2CAu;  // -1e30f
+  using MaxT = float;
+  static __device__ __forceinline__ MaxT max_init() { return -INFINITY; }
+  static __device__ __forceinline__ MaxT min_init() { return INFINITY; }
+  static __device__ __forceinline__ MaxT cmax(MaxT a, MaxT b) { return fmaxf(a, b); }
+  static __device__ __forceinline__ MaxT cmin(MaxT a, MaxT b) { return fminf(a, b); }
+  static __device__ __forceinline__ MaxT vmax(const uint4& v) {
+    return fmaxf(fmaxf(__uint_as_float(v.x), __uint_as_float(v.y)),
+                 fmaxf(__uint_as_float(v.z), __uint_as_float(v.w)));
+  }
+  static __device__ __forceinline__ MaxT vmin(const uint4& v) {
+    return fminf(fminf(__uint_as_float(v.x), __uint_as_float(v.y)),
+                 fminf(__uint_as_float(v.z), __uint_as_float(v.w)));
+  }
+  static __device__ __forceinline__ float max_f(MaxT m) { return m; }
+  static __device__ __forceinline__ float min_f(MaxT m) { return m; }
+  static __device__ __forceinline__ void unpack(const uint4& v, float (&x)[4]) {
+    x[0] = __uint_as_float(v.x);
+    x[1] = __uint_as_float(v.y);
+    x[2] = __uint_as_float(v.z);
+    x[3] = __uint_as_float(v.w);
+  }
+  static __device__ __forceinline__ uint4 pack(const float (&d)[4]) {
+    return make_uint4(__float_as_uint(d[0]), __float_as_uint(d[1]), __float_as_uint(d[2]),
+                      __float_as_uint(d[3]));
+  }
+  static __device__ __forceinline__ float load1(const void* base, int64_t i) {
+    return reinterpret_cast<const float*>(base)[i];
+  }
+};
 
 constexpr int kChunkVec = 256;            // 16-B vectors per full TMA chunk (8 warp-rows of 32)
 constexpr int kChunkBytes = kChunkVec * 16;
@@ -65,10 +178,9 @@ struct WarpStream {
   int c_stage;
   uint32_t c_par;
 
-  __device__ __forceinline__ void init(const void* base, int64_t ld_bytes, int V, int nrows,
+  __device__ __forceinline__ void init(const void* base, int64_t ld_bytes, int nvec, int nrows,
                                        unsigned char* my_data, uint64_t* my_bar, int warp,
                                        int lane) {
-    const int nvec = V >> 3;
     const int R = (nvec + 31) >> 5;
     const int q = R / WARPS, rem = R % WARPS;
     const int my_rows = q + (warp < rem ? 1 : 0);
@@ -157,14 +269,15 @@ struct WarpStream {
   }
 };
 
+template <typename E>
 struct LaneState {
   float negm, s0, s1, t0, t1;
-  uint32_t pmx, pmn;
+  typename E::MaxT pmx, pmn;
 };
 
-template <bool ENT>
-__device__ __forceinline__ void lazy_rescale(LaneState& L, uint32_t cm, float scale) {
-  const float cmf = fmaxf(bf16lo(cm), bf16hi(cm)) * scale;
+template <typename E, bool ENT>
+__device__ __forceinline__ void lazy_rescale(LaneState<E>& L, typename E::MaxT cm, float scale) {
+  const float cmf = E::max_f(cm) * scale;
   if (cmf + L.negm > kRescaleThr) {
     const float d = cmf + L.negm;  // new reference - old reference > 0
     const float f = ex2_approx(-d);
@@ -179,13 +292,14 @@ __device__ __forceinline__ void lazy_rescale(LaneState& L, uint32_t cm, float sc
   }
 }
 
-template <bool ENT>
-__device__ __forceinline__ void accumulate_vec(LaneState& L, const uint4& v, float scale) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+template <typename E, bool ENT>
+__device__ __forceinline__ void accumulate_vec(LaneState<E>& L, const uint4& v, float scale) {
+  float x[E::kPerVec];
+  E::unpack(v, x);
 #pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const float y0 = fmaf(bf16lo(w[j]), scale, L.negm);
-    const float y1 = fmaf(bf16hi(w[j]), scale, L.negm);
+  for (int j = 0; j < E::kPerVec; j += 2) {
+    const float y0 = fmaf(x[j], scale, L.negm);
+    const float y1 = fmaf(x[j + 1], scale, L.negm);
     const float e0 = ex2_approx(y0);
     const float e1 = ex2_approx(y1);
     L.s0 += e0;
@@ -197,25 +311,20 @@ __device__ __forceinline__ void accumulate_vec(LaneState& L, const uint4& v, flo
   }
 }
 
-__device__ __forceinline__ uint32_t max4(const uint4& v) {
-  return max_bf16x2(max_bf16x2(v.x, v.y), max_bf16x2(v.z, v.w));
-}
-__device__ __forceinline__ uint32_t min4(const uint4& v) {
-  return min_bf16x2(min_bf16x2(v.x, v.y), min_bf16x2(v.z, v.w));
-}
-
 // ------------------------------------------------------------------------------------------
-// forward, bf16, rows 16-B aligned
+// forward, rows 16-B aligned (bf16 / fp16 / fp32)
 // ------------------------------------------------------------------------------------------
-template <int WARPS, int STAGES, bool ENT, bool MINMAX>
+template <int DT, int WARPS, int STAGES, bool ENT, bool MINMAX>
 __global__ void __launch_bounds__(WARPS * 32, 1)
-logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
+logprob_fwd_kernel(const void* __restrict__ logits, int64_t ld,
                         const int64_t* __restrict__ labels, int T, int V, float scale,
                         float* __restrict__ logp, float* __restrict__ ent,
                         float* __restrict__ lse, float* __restrict__ rowmax,
                         float* __restrict__ rowmin) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FwdSmem<WARPS, STAGES>;
+  using E = Elem<DT>;
+  constexpr uint32_t kNeutral = E::kNeutralWord;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* part = reinterpret_cast<float*>(smem + L::kPartOff);   // [kSlots][6][WARPS]
   int* cnt = reinterpret_cast<int*>(smem + L::kCntOff);         // arrivals per slot
@@ -225,20 +334,20 @@ logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
 
   const int nrows = (T - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   WarpStream<WARPS, STAGES> ws;
-  ws.init(logits, ld * 2, V, nrows, smem + warp * STAGES * kChunkBytes,
+  ws.init(logits, ld * E::kBytes, V / E::kPerVec, nrows, smem + warp * STAGES * kChunkBytes,
           reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
 
   for (int it = 0; it < nrows; ++it) {
     const int row = blockIdx.x + it * gridDim.x;
-    // the label logit is a single 2-byte gather; one (rotating) warp fetches it early
+    // the label logit is a single-element gather; one (rotating) warp fetches it early
     float xy = 0.f;
     const bool fetch_xy = (it % WARPS) == warp && lane == 0;
     if (fetch_xy) {
       const int64_t lab = labels[row];
-      xy = (lab >= 0 && lab < V) ? __bfloat162float(logits[(int64_t)row * ld + lab])
+      xy = (lab >= 0 && lab < V) ? E::load1(logits, (int64_t)row * ld + lab)
                                  : __int_as_float(0x7fc00000);
     }
-    LaneState S{kSentinel, 0.f, 0.f, 0.f, 0.f, kNegInf2, kPosInf2};
+    LaneState<E> S{kSentinel, 0.f, 0.f, 0.f, 0.f, E::max_init(), E::min_init()};
 
     int left = ws.seg_len;
     while (left > 0) {
@@ -250,17 +359,17 @@ logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
 #pragma unroll
         for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
         ws.release(lane);
-        uint32_t cm = max4(v[0]);
+        typename E::MaxT cm = E::vmax(v[0]);
 #pragma unroll
-        for (int i = 1; i < 8; i++) cm = max_bf16x2(cm, max4(v[i]));
-        S.pmx = max_bf16x2(S.pmx, cm);
+        for (int i = 1; i < 8; i++) cm = E::cmax(cm, E::vmax(v[i]));
+        S.pmx = E::cmax(S.pmx, cm);
         if (MINMAX) {
 #pragma unroll
-          for (int i = 0; i < 8; i++) S.pmn = min_bf16x2(S.pmn, min4(v[i]));
+          for (int i = 0; i < 8; i++) S.pmn = E::cmin(S.pmn, E::vmin(v[i]));
         }
-        lazy_rescale<ENT>(S, cm, scale);
+        lazy_rescale<E, ENT>(S, cm, scale);
 #pragma unroll
-        for (int i = 0; i < 8; i++) accumulate_vec<ENT>(S, v[i], scale);
+        for (int i = 0; i < 8; i++) accumulate_vec<E, ENT>(S, v[i], scale);
       } else {
         // tail of the slice: 1..7 warp-rows, only the vocabulary's last one can be ragged
         const int nr = (nv + 31) >> 5;
@@ -269,11 +378,11 @@ logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
           const bool act = r * 32 + lane < nv;
           uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
           if (act) v = lds128(base + r * 512);
-          const uint32_t cm = max4(v);
-          S.pmx = max_bf16x2(S.pmx, cm);
-          if (MINMAX && act) S.pmn = min_bf16x2(S.pmn, min4(v));
-          lazy_rescale<ENT>(S, cm, scale);
-          accumulate_vec<ENT>(S, v, scale);
+          const typename E::MaxT cm = E::vmax(v);
+          S.pmx = E::cmax(S.pmx, cm);
+          if (MINMAX && act) S.pmn = E::cmin(S.pmn, E::vmin(v));
+          lazy_rescale<E, ENT>(S, cm, scale);
+          accumulate_vec<E, ENT>(S, v, scale);
         }
         ws.release(lane);
       }
@@ -290,8 +399,8 @@ logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
     if (ENT) Tt = warp_sum(f * fmaf(dl, s, t));
     float mx = 0.f, mn = 0.f;
     if (MINMAX) {
-      mx = warp_max(fmaxf(bf16lo(S.pmx), bf16hi(S.pmx)));
-      mn = warp_min(fminf(bf16lo(S.pmn), bf16hi(S.pmn)));
+      mx = warp_max(E::max_f(S.pmx));
+      mn = warp_min(E::min_f(S.pmn));
     }
     // ---- publish; the last warp to arrive finalises the row (no CTA-wide barrier) -----------
     const int slot = it & (kSlots - 1);
@@ -351,58 +460,45 @@ logprob_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
   }
 }
 
-// One warp-row group (8 vectors per lane) of the backward pass.
-template <bool HAS_GH>
+// One 16-byte vector of the backward pass.
+template <typename E, bool HAS_GH>
 __device__ __forceinline__ void bwd_vec(const uint4& v, int vi, bool act, float scale, float nlse2,
                                         float A0, float B0, float lab_add, int lvec, int lsub,
                                         char* out_row) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  float d[8];
+  float x[E::kPerVec], d[E::kPerVec];
+  E::unpack(v, x);
 #pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const float y0 = fmaf(bf16lo(w[j]), scale, nlse2);
-    const float y1 = fmaf(bf16hi(w[j]), scale, nlse2);
-    const float p0 = ex2_approx(y0);
-    const float p1 = ex2_approx(y1);
-    if (HAS_GH) {
-      d[2 * j] = p0 * fmaf(B0, y0, A0);
-      d[2 * j + 1] = p1 * fmaf(B0, y1, A0);
-    } else {
-      d[2 * j] = p0 * A0;
-      d[2 * j + 1] = p1 * A0;
-    }
+  for (int j = 0; j < E::kPerVec; j++) {
+    const float y = fmaf(x[j], scale, nlse2);
+    const float p = ex2_approx(y);
+    d[j] = HAS_GH ? p * fmaf(B0, y, A0) : p * A0;
   }
   if (vi == lvec) {  // the one-hot term of the label, one lane once per row
 #pragma unroll
-    for (int k = 0; k < 8; k++)
+    for (int k = 0; k < E::kPerVec; k++)
       if (k == lsub) d[k] += lab_add;
   }
-  if (act) {
-    uint4 o;
-    o.x = pack_bf16x2(d[0], d[1]);
-    o.y = pack_bf16x2(d[2], d[3]);
-    o.z = pack_bf16x2(d[4], d[5]);
-    o.w = pack_bf16x2(d[6], d[7]);
-    stg_na_v4(out_row + (int64_t)vi * 16, o);
-  }
+  if (act) stg_na_v4(out_row + (int64_t)vi * 16, E::pack(d));
 }
 
 // ------------------------------------------------------------------------------------------
-// backward, bf16, rows 16-B aligned (input and output)
+// backward, rows 16-B aligned on input and output (bf16 / fp16 / fp32)
 // ------------------------------------------------------------------------------------------
-template <int WARPS, int STAGES, bool HAS_GH>
+template <int DT, int WARPS, int STAGES, bool HAS_GH>
 __global__ void __launch_bounds__(WARPS * 32, 1)
-logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
+logprob_bwd_kernel(const void* __restrict__ logits, int64_t ld,
                         const int64_t* __restrict__ labels, const float* __restrict__ lse,
                         const float* __restrict__ entropy, const float* __restrict__ g_logp,
                         const float* __restrict__ g_ent, int T, int V, float scale,
-                        float inv_temp, __nv_bfloat16* __restrict__ dlogits, int64_t ld_out) {
+                        float inv_temp, void* __restrict__ dlogits, int64_t ld_out) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FwdSmem<WARPS, STAGES>;
+  using E = Elem<DT>;
+  constexpr uint32_t kNeutral = E::kNeutralWord;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nrows = (T - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   WarpStream<WARPS, STAGES> ws;
-  ws.init(logits, ld * 2, V, nrows, smem + warp * STAGES * kChunkBytes,
+  ws.init(logits, ld * E::kBytes, V / E::kPerVec, nrows, smem + warp * STAGES * kChunkBytes,
           reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
   if (ws.seg_len == 0) return;  // this warp owns no part of the row (tiny vocabularies)
 
@@ -421,8 +517,8 @@ logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
     lab_add = glp * inv_temp;
     const int64_t lab = labels[row];
     const bool ok = lab >= 0 && lab < V;
-    lvec = ok ? (int)(lab >> 3) : -1;
-    lsub = (int)(lab & 7);
+    lvec = ok ? (int)(lab / E::kPerVec) : -1;
+    lsub = (int)(lab % E::kPerVec);
   };
   float n_nlse2 = 0.f, n_A0 = 0.f, n_B0 = 0.f, n_lab = 0.f;
   int n_lvec = -1, n_lsub = 0;
@@ -433,7 +529,7 @@ logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
     const float nlse2 = n_nlse2, A0 = n_A0, B0 = n_B0, lab_add = n_lab;
     const int lvec = n_lvec, lsub = n_lsub;
     if (it + 1 < nrows) load_row(row + gridDim.x, n_nlse2, n_A0, n_B0, n_lab, n_lvec, n_lsub);
-    char* out_row = reinterpret_cast<char*>(dlogits) + ((int64_t)row * ld_out) * 2;
+    char* out_row = reinterpret_cast<char*>(dlogits) + ((int64_t)row * ld_out) * E::kBytes;
 
     int left = ws.seg_len;
     int v0 = ws.sv + lane;  // global 16-B vector index of this lane's first vector in the chunk
@@ -448,7 +544,7 @@ logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
         ws.release(lane);
 #pragma unroll
         for (int i = 0; i < 8; i++)
-          bwd_vec<HAS_GH>(v[i], v0 + i * 32, true, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+          bwd_vec<E, HAS_GH>(v[i], v0 + i * 32, true, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
       } else {
         const int nr = (nv + 31) >> 5;
 #pragma unroll 1
@@ -456,7 +552,7 @@ logprob_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld,
           const bool act = r * 32 + lane < nv;
           uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
           if (act) v = lds128(base + r * 512);
-          bwd_vec<HAS_GH>(v, v0 + r * 32, act, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+          bwd_vec<E, HAS_GH>(v, v0 + r * 32, act, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
         }
         ws.release(lane);
       }
@@ -583,19 +679,57 @@ int set_smem(K kernel, int bytes) {
 constexpr int kWarps = 16;
 constexpr int kStages = 3;
 
-template <bool ENT, bool MINMAX>
+template <int DT, bool ENT, bool MINMAX>
 int launch_fwd_fast(const void* logits, int64_t ld, const int64_t* labels, int T, int V,
                     float scale, float* logp, float* ent, float* lse, float* rowmax,
                     float* rowmin, cudaStream_t st) {
-  auto k = logprob_fwd_bf16_kernel<kWarps, kStages, ENT, MINMAX>;
+  auto k = logprob_fwd_kernel<DT, kWarps, kStages, ENT, MINMAX>;
   constexpr int smem = FwdSmem<kWarps, kStages>::kBytes;
   int rc = set_smem(k, smem);
   if (rc) return rc;
   const int grid = min(T, sm_count());
-  k<<<grid, kWarps * 32, smem, st>>>((const __nv_bfloat16*)logits, ld, labels, T, V, scale, logp,
-                                     ent, lse, rowmax, rowmin);
-  return check_launch("logprob_fwd_bf16_kernel");
+  k<<<grid, kWarps * 32, smem, st>>>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin);
+  return check_launch("logprob_fwd_kernel");
 }
+
+template <int DT>
+int dispatch_fwd_fast(const void* logits, int64_t ld, const int64_t* labels, int T, int V,
+                      float scale, float* logp, float* ent, float* lse, float* rowmax,
+                      float* rowmin, cudaStream_t st) {
+  const bool mm = rowmax != nullptr || rowmin != nullptr;
+  if (ent) {
+    return mm ? launch_fwd_fast<DT, true, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st)
+              : launch_fwd_fast<DT, true, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st);
+  }
+  return mm ? launch_fwd_fast<DT, false, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st)
+            : launch_fwd_fast<DT, false, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st);
+}
+
+template <int DT, bool HAS_GH>
+int launch_bwd_fast(const void* logits, int64_t ld, const int64_t* labels, const float* lse,
+                    const float* entropy, const float* g_logp, const float* g_ent, int T, int V,
+                    float scale, float inv_temp, void* dlogits, int64_t ld_out, cudaStream_t st) {
+  auto k = logprob_bwd_kernel<DT, kWarps, kStages, HAS_GH>;
+  constexpr int smem = FwdSmem<kWarps, kStages>::kBytes;
+  int rc = set_smem(k, smem);
+  if (rc) return rc;
+  const int grid = min(T, sm_count());
+  k<<<grid, kWarps * 32, smem, st>>>(logits, ld, labels, lse, entropy, g_logp, g_ent, T, V, scale,
+                                     inv_temp, dlogits, ld_out);
+  return check_launch("logprob_bwd_kernel");
+}
+
+template <int DT>
+int dispatch_bwd_fast(const void* logits, int64_t ld, const int64_t* labels, const float* lse,
+                      const float* entropy, const float* g_logp, const float* g_ent, int T, int V,
+                      float scale, float inv_temp, void* dlogits, int64_t ld_out, cudaStream_t st) {
+  return g_ent ? launch_bwd_fast<DT, true>(logits, ld, labels, lse, entropy, g_logp, g_ent, T, V, scale,
+                                           inv_temp, dlogits, ld_out, st)
+               : launch_bwd_fast<DT, false>(logits, ld, labels, lse, entropy, g_logp, g_ent, T, V, scale,
+                                            inv_temp, dlogits, ld_out, st);
+}
+
+inline int per_vec(int dtype) { return dtype == B200RL_FP32 ? 4 : 8; }
 
 }  // namespace
 }  // namespace b200rl
@@ -615,20 +749,19 @@ int b200rl_logprob_entropy_fwd(const void* logits, int dtype, int64_t ld, const 
   B200RL_REQUIRE(logits && labels && logp && lse, "null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   const float scale = (float)(1.4426950408889634 / (double)temperature);
-  const bool fast = dtype == B200RL_BF16 && (V % 8 == 0) && (ld % 8 == 0) &&
-                    (reinterpret_cast<uintptr_t>(logits) % 16 == 0);
+  B200RL_REQUIRE(dtype == B200RL_BF16 || dtype == B200RL_FP16 || dtype == B200RL_FP32,
+                 "unsupported logits dtype code %d", dtype);
+  const int pv = per_vec(dtype);
+  const bool fast = (V % pv == 0) && (ld % pv == 0) && (reinterpret_cast<uintptr_t>(logits) % 16 == 0);
   if (fast) {
-    const bool mm = rowmax != nullptr || rowmin != nullptr;
-    if (entropy) {
-      return mm ? launch_fwd_fast<true, true>(logits, ld, labels, (int)T, (int)V, scale, logp,
-                                              entropy, lse, rowmax, rowmin, st)
-                : launch_fwd_fast<true, false>(logits, ld, labels, (int)T, (int)V, scale, logp,
-                                               entropy, lse, rowmax, rowmin, st);
+    switch (dtype) {
+      case B200RL_BF16:
+        return dispatch_fwd_fast<B200RL_BF16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, st);
+      case B200RL_FP16:
+        return dispatch_fwd_fast<B200RL_FP16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, st);
+      default:
+        return dispatch_fwd_fast<B200RL_FP32>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, st);
     }
-    return mm ? launch_fwd_fast<false, true>(logits, ld, labels, (int)T, (int)V, scale, logp,
-                                             entropy, lse, rowmax, rowmin, st)
-              : launch_fwd_fast<false, false>(logits, ld, labels, (int)T, (int)V, scale, logp,
-                                              entropy, lse, rowmax, rowmin, st);
   }
   const unsigned grid = (unsigned)T;
   switch (dtype) {
@@ -666,28 +799,21 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
   cudaStream_t st = (cudaStream_t)stream;
   const float scale = (float)(1.4426950408889634 / (double)temperature);
   const float inv_temp = (float)(1.0 / (double)temperature);
-  const bool fast = dtype == B200RL_BF16 && (V % 8 == 0) && (ld % 8 == 0) && (ld_out % 8 == 0) &&
+  B200RL_REQUIRE(dtype == B200RL_BF16 || dtype == B200RL_FP16 || dtype == B200RL_FP32,
+                 "unsupported logits dtype code %d", dtype);
+  const int pv = per_vec(dtype);
+  const bool fast = (V % pv == 0) && (ld % pv == 0) && (ld_out % pv == 0) &&
                     (reinterpret_cast<uintptr_t>(logits) % 16 == 0) &&
                     (reinterpret_cast<uintptr_t>(dlogits) % 16 == 0);
   if (fast) {
-    constexpr int smem = FwdSmem<kWarps, kStages>::kBytes;
-    const int grid = min((int)T, sm_count());
-    if (g_ent) {
-      auto k = logprob_bwd_bf16_kernel<kWarps, kStages, true>;
-      int rc = set_smem(k, smem);
-      if (rc) return rc;
-      k<<<grid, kWarps * 32, smem, st>>>((const __nv_bfloat16*)logits, ld, labels, lse, entropy,
-                                         g_logp, g_ent, (int)T, (int)V, scale, inv_temp,
-                                         (__nv_bfloat16*)dlogits, ld_out);
-    } else {
-      auto k = logprob_bwd_bf16_kernel<kWarps, kStages, false>;
-      int rc = set_smem(k, smem);
-      if (rc) return rc;
-      k<<<grid, kWarps * 32, smem, st>>>((const __nv_bfloat16*)logits, ld, labels, lse, entropy,
-                                         g_logp, g_ent, (int)T, (int)V, scale, inv_temp,
-                                         (__nv_bfloat16*)dlogits, ld_out);
+    switch (dtype) {
+      case B200RL_BF16:
+        return dispatch_bwd_fast<B200RL_BF16>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, st);
+      case B200RL_FP16:
+        return dispatch_bwd_fast<B200RL_FP16>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, st);
+      default:
+        return dispatch_bwd_fast<B200RL_FP32>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, st);
     }
-    return check_launch("logprob_bwd_bf16_kernel");
   }
   const unsigned grid = (unsigned)T;
   switch (dtype) {

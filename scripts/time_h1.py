@@ -46,3 +46,22 @@ bench("bwd (with g_ent)", lambda x: pkg.ops.logprob_entropy_bwd(x, y, lse, ent, 
 d = torch.empty_like(xs[0])
 bench("torch copy_ (reference)", lambda x: d.copy_(x), 4.0 * T * V)
 bench("torch sum fp32 (read-only)", lambda x: x.view(torch.int32).sum(), 2.0 * T * V)
+
+# fp32 logits (Megatron path): 4*V bytes per token forward, 8*V backward
+T32 = 4096
+x32 = [xs[i][:T32].float() for i in range(2)]
+y32, g32 = y[:T32], g[:T32]
+def bench32(name, fn, bytes_per_call, iters=8):
+    for i in range(2): fn(x32[i % 2])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters): fn(x32[i % 2])
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    print(f"{name:28s} {ms*1e3:9.1f} us  {bytes_per_call/ms/1e6:8.0f} GB/s  {bytes_per_call/ms/1e6/PEAK:6.3f} of measured copy peak")
+def f32(x):
+    global lse, ent
+    out = pkg.ops.logprob_entropy_fwd(x, y32, 1.0, True, False); lse, ent = out[2], out[1]
+bench32("fp32 fwd (+entropy)", f32, 4.0 * T32 * V)
+bench32("fp32 bwd", lambda x: pkg.ops.logprob_entropy_bwd(x, y32, lse, ent, g32, None, 1.0), 8.0 * T32 * V)

@@ -96,6 +96,34 @@ def test_vs_oracle_seeded(T, V, temp, cuda):
     _close(xg2.grad, xc2.grad.float().numpy(), rtol=G_RTOL, atol=1e-6, msg="dlogits (no entropy grad)")
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
+@pytest.mark.parametrize("T,V,temp", [(5, 64, 1.0), (37, 4100, 0.7), (66, 151936, 1.0), (3, 152064, 1.3)])
+def test_fp16_fp32_fast_path(dtype, T, V, temp, cuda):
+    """The TMA kernels instantiated for fp16 and fp32 logits (the Megatron engine hands the loss
+    function fp32 logits: areal/experimental/megatron_engine.py:510-521)."""
+    from areal_vllm_b200 import functional as BF
+    from oracle import torch_ref
+
+    gen = torch.Generator().manual_seed(T * 7 + V)
+    x = (torch.randn(T, V, generator=gen) * 2)
+    labels = torch.randint(0, V, (T,), generator=gen)
+    x[torch.arange(0, T, 2), labels[::2]] += 6.0
+    x = x.to(dtype)
+    g_lp, g_ent = torch.randn(T, generator=gen), 0.05 * torch.randn(T, generator=gen)
+    xc = x.clone().requires_grad_(True)
+    lp_r, ent_r = torch_ref.logprobs_entropy(xc, labels, temp)
+    (lp_r * g_lp).sum().add((ent_r * g_ent).sum()).backward()
+    xg = x.to(cuda).requires_grad_(True)
+    lp, ent, vmax, vmin = BF.gather_logprobs_entropy_minmax(xg, labels.to(cuda), temp)
+    (lp * g_lp.to(cuda)).sum().add((ent * g_ent.to(cuda)).sum()).backward()
+    _close(lp, lp_r.detach().numpy(), msg="logp")
+    _close(ent, ent_r.detach().numpy(), msg="entropy")
+    assert xg.grad.dtype == dtype
+    tol = 1e-4 if dtype == torch.float32 else 2.0 ** -10  # one ulp of fp16 is 2^-11 relative
+    _close(xg.grad, xc.grad.float().numpy(), rtol=tol, atol=1e-6, msg="dlogits")
+    assert torch.equal(vmax.cpu(), x.float().max(-1).values) and torch.equal(vmin.cpu(), x.float().min(-1).values)
+
+
 def test_extreme_rows(cuda):
     """Rows that force the lazy rescale: a huge late maximum, a strongly negative start, constant
     rows, and a vocabulary-sized spike; plus -inf entries (masked vocabulary)."""
