@@ -15,12 +15,55 @@ import torch.distributed as dist
 from . import functional, ops
 
 __all__ = [
+    "padded_gae",
     "AdvNorm",
     "grpo_loss_fn",
     "group_advantage_stats",
     "ppo_actor_loss_fn_fused_advnorm",
     "group_reward_norm",
 ]
+
+
+@torch.no_grad()
+def padded_gae(
+    rewards: torch.Tensor,
+    values: torch.Tensor,
+    seq_no_eos_mask: torch.Tensor,
+    gamma: float,
+    lam: float,
+) -> torch.Tensor:
+    """The padded ``[B, L]`` GAE of ``PPOActor.compute_advantages`` (ref actor.py:131-148), which
+    the reference evaluates with a python loop over ``L-1`` time steps (~5 launches per step):
+
+        for t in reversed(range(L - 1)):
+            nextvalues = values[:, t + 1] * (seq_no_eos_mask if t == L - 2 else 1)
+            delta = rewards[:, t] + gamma * nextvalues - values[:, t]
+            lastgaelam = delta + gamma * lam * lastgaelam
+
+    and returns ``[B, L]`` advantages whose last column is zero. A row of the padded tensors IS a
+    packed "misaligned" sequence: ``L-1`` rewards against ``L`` values, so the whole batch is one
+    call of the packed GAE kernel with ``cu_seqlens = arange(B+1) * (L-1)`` and
+    ``bootstrap = seq_no_eos_mask`` — no new kernel, one launch instead of ``5 * (L-1)``.
+    Unlike the reference loop this does not zero ``values[:, -1]`` in place where the mask is 0.
+    """
+    if rewards.dim() != 2 or rewards.shape != values.shape:
+        raise RuntimeError("rewards and values must both be [B, L]")
+    B, L = rewards.shape
+    out = torch.zeros((B, L), dtype=torch.float32, device=rewards.device)
+    if L < 2 or B == 0:
+        return out
+    cu = torch.arange(B + 1, dtype=torch.int32, device=rewards.device) * (L - 1)
+    adv, _ = ops.gae_1d_nolp_misalign(
+        rewards[:, : L - 1].float().contiguous().view(-1),
+        values.float().contiguous().view(-1),
+        cu,
+        seq_no_eos_mask.bool().contiguous(),
+        float(gamma),
+        float(lam),
+        0,
+    )
+    out[:, : L - 1] = adv.view(B, L - 1)
+    return out
 
 
 class AdvNorm:

@@ -204,6 +204,36 @@ def gen_gae(P):
         print("wrote", name, total, "tokens")
 
 
+def gen_padded_gae():
+    """The padded GAE loop of PPOActor.compute_advantages (areal/engine/ppo/actor.py:131-148),
+    executed from the reference source lines themselves."""
+    import textwrap
+
+    lines = open(os.path.join(R.REF_ROOT, "areal/engine/ppo/actor.py")).read().splitlines()[130:148]
+    code = textwrap.dedent("\n".join(lines))
+    d = {}
+    for k, (B, L, gamma, lam) in enumerate([(6, 33, 1.0, 1.0), (9, 130, 0.99, 0.95)]):
+        gen = torch.Generator().manual_seed(300 + k)
+        lens = torch.randint(3, L + 1, (B,), generator=gen)
+        lens[0] = L
+        att = torch.arange(L)[None, :] < lens[:, None]
+        rewards = torch.randn(B, L, generator=gen) * att
+        values = torch.randn(B, L, generator=gen) * att
+        no_eos = lens == L
+
+        class Self:
+            discount, gae_lambda = gamma, lam
+
+        ns = dict(torch=torch, rewards=rewards, bs=B, max_seqlen=L, seq_no_eos_mask=no_eos,
+                  self=Self, data={"values": values.clone()})
+        exec(code, ns)
+        d[f"rewards_{k}"], d[f"values_{k}"], d[f"no_eos_{k}"] = rewards.numpy(), values.numpy(), no_eos.numpy()
+        d[f"gamma_{k}"], d[f"lam_{k}"] = np.float64(gamma), np.float64(lam)
+        d[f"adv_{k}"] = ns["advantages"].numpy()
+    np.savez_compressed(os.path.join(OUT, "gae_padded.npz"), **d)
+    print("wrote gae_padded")
+
+
 def _ref_make_intervals():
     path = os.path.join(R.REF_ROOT, "realhf/tests/cpp_extensions/test_interval_ops.py")
     tree = ast.parse(open(path).read())
@@ -280,6 +310,7 @@ def main():
     gen_h2_legacy(P)
     gen_advnorm(F, R.adv_norm_class())
     gen_gae(P)
+    gen_padded_gae()
     gen_intervals()
 
 

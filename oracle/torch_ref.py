@@ -219,3 +219,21 @@ def group_reward_norm(reward_score: torch.Tensor, group_size: int) -> torch.Tens
         r = reward_score[s]
         out[s] = (r - r.mean()) / (r.std() + 1e-9)
     return out
+
+
+@torch.no_grad()
+def padded_gae(rewards, values, seq_no_eos_mask, gamma, lam):
+    """The padded GAE loop of PPOActor.compute_advantages (areal/engine/ppo/actor.py:131-148),
+    on a copy of ``values`` (the reference's ``nextvalues *= mask`` writes through a view)."""
+    values = values.clone()
+    bs, max_seqlen = rewards.shape
+    rev = [torch.zeros(bs, dtype=torch.float32, device=values.device)]          # :136-138
+    last = 0
+    for t in reversed(range(max_seqlen - 1)):                                   # :140
+        nxt = values[:, t + 1]                                                  # :141
+        if t == max_seqlen - 2:
+            nxt *= seq_no_eos_mask                                              # :142-143
+        delta = rewards[:, t] + gamma * nxt - values[:, t]                      # :144
+        last = delta + gamma * lam * last                                       # :145
+        rev.append(last)                                                        # :146
+    return torch.stack(rev[::-1], dim=1)                                        # :147

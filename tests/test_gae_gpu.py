@@ -12,7 +12,8 @@ from conftest import GOLDEN, load_golden
 
 pytestmark = pytest.mark.gpu
 
-GAE = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "gae_*.npz")))
+GAE = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "gae_*.npz"))
+             if "padded" not in p)
 
 
 def _run(g_or_tuple, cuda, mode):
@@ -146,3 +147,36 @@ def test_edge_cases(cuda):
                                                 torch.from_numpy(cu).long().to(cuda),
                                                 torch.from_numpy(b).to(cuda))
     np.testing.assert_allclose(a.cpu().numpy(), cpu_ref.gae_py(r, v, cu, b, 0.97, 0.9)[0], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("gl", [(1.0, 1.0), (0.99, 0.95)])
+def test_padded_gae_adapter(gl, cuda):
+    """actor.padded_gae (the [B, L] GAE of compute_advantages, actor.py:131-148) vs the oracle loop."""
+    from areal_vllm_b200.actor import padded_gae
+    from oracle import torch_ref
+
+    gen = torch.Generator().manual_seed(8)
+    B, L = 37, 301
+    lens = torch.randint(5, L + 1, (B,), generator=gen)
+    att = torch.arange(L)[None, :] < lens[:, None]
+    rewards = torch.randn(B, L, generator=gen) * att
+    values = torch.randn(B, L, generator=gen) * att
+    no_eos = lens == L
+    ref = torch_ref.padded_gae(rewards, values, no_eos, *gl)
+    v0 = values.clone().to(cuda)
+    out = padded_gae(rewards.to(cuda), v0, no_eos.to(cuda), *gl)
+    assert out.shape == (B, L) and out.dtype == torch.float32
+    assert torch.equal(v0.cpu(), values)  # inputs untouched
+    np.testing.assert_allclose(out.cpu().numpy(), ref.numpy(), rtol=1e-5, atol=1e-5)
+    assert float(out[:, -1].abs().max()) == 0.0
+
+
+def test_padded_gae_golden(cuda):
+    from areal_vllm_b200.actor import padded_gae
+
+    g = load_golden("gae_padded")
+    for k in range(2):
+        t = lambda a: torch.from_numpy(a).to(cuda)
+        out = padded_gae(t(g[f"rewards_{k}"]), t(g[f"values_{k}"]), t(g[f"no_eos_{k}"]),
+                         float(g[f"gamma_{k}"]), float(g[f"lam_{k}"]))
+        np.testing.assert_allclose(out.cpu().numpy(), g[f"adv_{k}"], rtol=1e-5, atol=1e-5)
