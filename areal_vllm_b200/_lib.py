@@ -14,7 +14,7 @@ from ctypes import c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_void_
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200rl.so")
+LIB_PATH = os.environ.get("B200RL_LIB") or os.path.join(_HERE, "libb200rl.so")  # override: tuning builds
 
 BF16, FP16, FP32 = 0, 1, 2
 DTYPE_CODE = {torch.bfloat16: BF16, torch.float16: FP16, torch.float32: FP32}

@@ -28,7 +28,10 @@ namespace {
 
 // ============================ SERIAL =========================================
 constexpr int kSerWarps = 4;
-constexpr int kSerBlk = 128;  // tokens per warp iteration
+constexpr int kSerPerLane = 8;               // tokens per lane per block
+constexpr int kSerBlk = 32 * kSerPerLane;    // 256 tokens per warp iteration: the 4-cycle/token
+                                             // chain of one block (~1000 cycles) covers the DRAM
+                                             // latency of the next block's prefetch
 
 __global__ void __launch_bounds__(kSerWarps * 32)
 gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
@@ -48,11 +51,11 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
     const bool bs = boot[i] != 0;
     float X = 0.f;  // lastgae
     // software prefetch of the first block
-    float r[4], v[4], vn[4];
+    float r[kSerPerLane], v[kSerPerLane], vn[kSerPerLane];
     int hi = n;
     int lo = max(hi - kSerBlk, 0);
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
+    for (int k = 0; k < kSerPerLane; k++) {
       int u = lo + 32 * k + lane;
       bool ok = u < hi;
       r[k] = ok ? rewards[rs + u] : 0.f;
@@ -62,9 +65,9 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
     while (hi > 0) {
       const int cnt = hi - lo;
       // delta in the reference's contraction: fma(gamma, next_v, r) - v   (gae.cu:22-23)
-      float vk[4];
+      float vk[kSerPerLane];
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
+      for (int k = 0; k < kSerPerLane; k++) {
         int u = lo + 32 * k + lane;
         float nv = (u == n - 1 && !bs) ? 0.f : vn[k];
         float dl = __fsub_rn(__fmaf_rn(gamma, nv, r[k]), v[k]);
@@ -74,7 +77,7 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
       // prefetch next block (to the left) while the chain runs
       const int nhi = lo, nlo = max(lo - kSerBlk, 0);
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
+      for (int k = 0; k < kSerPerLane; k++) {
         int u = nlo + 32 * k + lane;
         bool ok = u < nhi;
         r[k] = ok ? rewards[rs + u] : 0.f;
@@ -84,32 +87,42 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
       __syncwarp();
       if (lane == 0) {
         int q = cnt - 1;
-        // ragged top down to a multiple of 4, then 4 tokens per step with 16-B smem accesses; the
-        // next group is loaded before the current one is chained, so only the 4 dependent FMAs
-        // (4 cycles each) sit on the critical path
-        for (; (q & 3) != 3 && q >= 0; q--) {
+        // ragged top down to a multiple of 8, then 8 tokens per step with two 16-B smem loads that
+        // are issued one step (8 dependent FMAs = 32 cycles) ahead, which covers the ~29-cycle
+        // shared-memory latency: only the FMA chain is on the critical path
+        for (; (q & 7) != 7 && q >= 0; q--) {
           X = __fmaf_rn(c, X, d[q]);
           d[q] = X;
         }
-        if (q >= 3) {
-          float4 cur = *reinterpret_cast<float4*>(d + q - 3);
-#pragma unroll 4
-          for (; q >= 3; q -= 4) {
-            float4 nxt = cur;
-            if (q >= 7) nxt = *reinterpret_cast<float4*>(d + q - 7);
-            cur.w = X = __fmaf_rn(c, X, cur.w);
-            cur.z = X = __fmaf_rn(c, X, cur.z);
-            cur.y = X = __fmaf_rn(c, X, cur.y);
-            cur.x = X = __fmaf_rn(c, X, cur.x);
-            *reinterpret_cast<float4*>(d + q - 3) = cur;
-            cur = nxt;
+        if (q >= 7) {
+          float4 hi4 = *reinterpret_cast<float4*>(d + q - 3);
+          float4 lo4 = *reinterpret_cast<float4*>(d + q - 7);
+#pragma unroll 2
+          for (; q >= 7; q -= 8) {
+            float4 nhi = hi4, nlo = lo4;
+            if (q >= 15) {
+              nhi = *reinterpret_cast<float4*>(d + q - 11);
+              nlo = *reinterpret_cast<float4*>(d + q - 15);
+            }
+            hi4.w = X = __fmaf_rn(c, X, hi4.w);
+            hi4.z = X = __fmaf_rn(c, X, hi4.z);
+            hi4.y = X = __fmaf_rn(c, X, hi4.y);
+            hi4.x = X = __fmaf_rn(c, X, hi4.x);
+            lo4.w = X = __fmaf_rn(c, X, lo4.w);
+            lo4.z = X = __fmaf_rn(c, X, lo4.z);
+            lo4.y = X = __fmaf_rn(c, X, lo4.y);
+            lo4.x = X = __fmaf_rn(c, X, lo4.x);
+            *reinterpret_cast<float4*>(d + q - 3) = hi4;
+            *reinterpret_cast<float4*>(d + q - 7) = lo4;
+            hi4 = nhi;
+            lo4 = nlo;
           }
         }
       }
       __syncwarp();
       X = __shfl_sync(0xffffffffu, X, 0);
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
+      for (int k = 0; k < kSerPerLane; k++) {
         int u = lo + 32 * k + lane;
         if (u < hi) {
           float A = d[32 * k + lane];
