@@ -15,6 +15,7 @@ import torch.distributed as dist
 from . import functional, ops
 
 __all__ = [
+    "grpo_loss_fn_fused",
     "padded_gae",
     "AdvNorm",
     "grpo_loss_fn",
@@ -266,6 +267,96 @@ def group_reward_norm(reward_score: torch.Tensor, group_size: int) -> torch.Tens
     return out
 
 
+def grpo_loss_fn_fused(
+    logits: torch.Tensor,
+    input_data: Dict,
+    temperature: float,
+    eps_clip: float,
+    eps_clip_higher: float | None,
+    c_clip: float | None,
+    behav_imp_weight_cap: float | None,
+    loss_scale: Optional[torch.Tensor] = None,
+    stats: Optional[Dict] = None,
+):
+    """``grpo_loss_fn`` and its ``backward()`` in one pass over the logits (4*V instead of 6*V bytes
+    of HBM traffic per token; see csrc/grpo_fused.cu).
+
+    Same inputs as ``grpo_loss_fn`` plus ``loss_scale``: the factor the engine multiplies the loss
+    by before ``backward()`` (``loss_weight_fn(mb) / total_loss_weight * dp_world_size``,
+    fsdp_engine.py:543-547 — it does not depend on the loss, so compute it first and pass it in).
+    Returns ``loss * loss_scale``; do NOT multiply again. ``logits.grad`` is produced during this
+    call and handed out by ``backward()``; if the gradient that arrives there is not 1 the stored
+    gradient is rescaled in place, so the result is right (just slower) for any caller.
+    Falls back to ``grpo_loss_fn`` for layouts the fused kernel does not take."""
+    from . import ops as _ops
+
+    input_ids = input_data["input_ids"]
+    old_logp = input_data["logprobs"]
+    advantages = input_data["advantages"]
+    loss_mask = input_data["loss_mask"].bool()
+    prox_logp = input_data["prox_logp"]
+    want_stats = stats is not None or _stats_tracker() is not None
+    out = None
+    if logits.is_cuda and logits.dim() == 2 and logits.requires_grad and torch.is_grad_enabled() \
+            and not torch.compiler.is_compiling():
+        labels = torch.roll(input_ids, shifts=-1, dims=-1)
+        if c_clip is not None:
+            assert c_clip > 1.0, c_clip
+        up = None
+        if loss_scale is not None:
+            up = loss_scale if isinstance(loss_scale, torch.Tensor) else torch.tensor(
+                float(loss_scale), dtype=torch.float32, device=logits.device)
+        out = _ops._raw_grpo_fused_step(
+            logits.detach(), labels, prox_logp, old_logp, advantages, loss_mask, float(temperature),
+            1.0 - eps_clip, 1.0 + (eps_clip if eps_clip_higher is None else eps_clip_higher),
+            -1.0 if c_clip is None else float(c_clip),
+            -1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap), up, want_stats)
+    if out is None:
+        loss = grpo_loss_fn(logits, input_data, temperature, eps_clip, eps_clip_higher, c_clip,
+                            behav_imp_weight_cap, stats=stats)
+        return loss * loss_scale if loss_scale is not None else loss
+    loss = _ops._GrpoFusedFn.apply(logits, out["loss"], out["dlogits"], up)
+    if want_stats:
+        clip_mask = out["s_clip"].view(torch.bool)
+        dual = out["s_dual"].view(torch.bool)
+        collected = dict(
+            n_valid_tokens=loss_mask, clipped_tokens=clip_mask, dual_clipped_tokens=dual,
+            importance_weight=out["s_iw"], approx_kl=out["s_kl"], new_logp=out["logp"],
+            old_logp=old_logp, entropy=out["entropy"], actor_loss=out["s_loss"],
+            clip_ratio=clip_mask.float(), dual_clip_ratio=dual.float(),
+            unclipped_behave_tokens=out["s_bm"].view(torch.bool), behave_imp_weight=out["s_bw"],
+            behave_approx_kl=out["s_bkl"], vocab_min_logits=out["rowmin"], vocab_max_logits=out["rowmax"],
+            clipped_new_logp=torch.where(clip_mask, out["logp"], 0.0),
+            clipped_old_logp=torch.where(clip_mask, old_logp, 0.0),
+        )
+        if stats is not None:
+            stats.update(collected)
+        _register_stats(_stats_tracker(), logits, collected)
+    return loss
+
+
+def _register_stats(st, logits, c):
+    if st is None:
+        return
+    st.denominator(
+        n_tokens=torch.ones(logits.shape[0], dtype=torch.bool, device=logits.device),
+        n_valid_tokens=c["n_valid_tokens"], clipped_tokens=c["clipped_tokens"],
+        dual_clipped_tokens=c["dual_clipped_tokens"],
+    )
+    st.stat(
+        importance_weight=c["importance_weight"], approx_kl=c["approx_kl"], new_logp=c["new_logp"],
+        old_logp=c["old_logp"], entropy=c["entropy"], actor_loss=c["actor_loss"],
+        clip_ratio=c["clip_ratio"], dual_clip_ratio=c["dual_clip_ratio"], denominator="n_valid_tokens",
+    )
+    st.denominator(unclipped_behave_tokens=c["unclipped_behave_tokens"])
+    st.stat(behave_imp_weight=c["behave_imp_weight"], behave_approx_kl=c["behave_approx_kl"],
+            denominator="unclipped_behave_tokens")
+    st.stat(vocab_min_logits=c["vocab_min_logits"], vocab_max_logits=c["vocab_max_logits"],
+            denominator="n_tokens")
+    st.stat(clipped_new_logp=c["clipped_new_logp"], clipped_old_logp=c["clipped_old_logp"],
+            denominator="clipped_tokens")
+
+
 def _stats_tracker():
     try:  # the reference's tracker, when this module is used inside AReaL
         from areal.utils import stats_tracker  # type: ignore
@@ -340,38 +431,5 @@ def grpo_loss_fn(
     )
     if stats is not None:
         stats.update(collected)
-    if st is not None:
-        st.denominator(
-            n_tokens=torch.ones(logits.shape[0], dtype=torch.bool, device=logits.device),
-            n_valid_tokens=collected["n_valid_tokens"],
-            clipped_tokens=collected["clipped_tokens"],
-            dual_clipped_tokens=collected["dual_clipped_tokens"],
-        )
-        st.stat(
-            importance_weight=collected["importance_weight"],
-            approx_kl=collected["approx_kl"],
-            new_logp=collected["new_logp"],
-            old_logp=collected["old_logp"],
-            entropy=collected["entropy"],
-            actor_loss=collected["actor_loss"],
-            clip_ratio=collected["clip_ratio"],
-            dual_clip_ratio=collected["dual_clip_ratio"],
-            denominator="n_valid_tokens",
-        )
-        st.denominator(unclipped_behave_tokens=collected["unclipped_behave_tokens"])
-        st.stat(
-            behave_imp_weight=collected["behave_imp_weight"],
-            behave_approx_kl=collected["behave_approx_kl"],
-            denominator="unclipped_behave_tokens",
-        )
-        st.stat(
-            vocab_min_logits=collected["vocab_min_logits"],
-            vocab_max_logits=collected["vocab_max_logits"],
-            denominator="n_tokens",
-        )
-        st.stat(
-            clipped_new_logp=collected["clipped_new_logp"],
-            clipped_old_logp=collected["clipped_old_logp"],
-            denominator="clipped_tokens",
-        )
+    _register_stats(st, logits, collected)
     return loss

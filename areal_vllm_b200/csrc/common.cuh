@@ -153,6 +153,13 @@ __device__ __forceinline__ void stg_na_v4(void* p, uint4 v) {
                : "memory");
 }
 
+// 16-B streaming store with an explicit L2 eviction policy
+__device__ __forceinline__ void stg_hint_v4(void* p, uint4 v, uint64_t policy) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p),
+               "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(policy)
+               : "memory");
+}
+
 // ---- warp reductions ------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -1,0 +1,496 @@
+// Fused GRPO actor step: logits -> log-prob, entropy, row max/min, clipped decoupled-PPO loss with
+// all its statistics, AND dlogits, in one kernel and one trip of the logits through HBM.
+//
+// The reference (and the drop-in path of this library) does forward and backward as separate
+// passes: 2*V bytes read, then 2*V read again + 2*V written = 6*V bytes per token. But the PPO
+// loss is separable per token once the number of valid tokens N is known, so the gradient of the
+// loss w.r.t. a token's log-prob is available the moment that token's row statistics are. Here a
+// CTA therefore streams a row from HBM for the forward statistics, finishes the token's loss
+// math, and immediately streams the SAME row again for the backward — now out of the 126 MB L2
+// (148 rows in flight are 45 MB) — writing dlogits. HBM traffic drops to 4*V bytes per token.
+//
+// What makes this legal is knowing the upstream gradient of the loss before backward() runs:
+// AReaL's engine multiplies the loss by a `loss_scale` that does not depend on the loss
+// (areal/engine/fsdp_engine.py:543-549), so it can be handed to this kernel up front; the
+// autograd node's backward then only checks that the incoming gradient is 1 and rescales
+// dlogits in place if it is not (b200rl_scale_inplace: no traffic when the factor is 1).
+//
+// Bound: HBM, 4*V bytes per token (bf16); L2 sees 6*V.
+#include "logprob_common.cuh"
+#include "ppo_math.cuh"
+
+namespace b200rl {
+namespace {
+
+using namespace lp;
+
+#ifndef B200RL_FUSED_WARPS
+#define B200RL_FUSED_WARPS 16
+#endif
+#ifndef B200RL_FUSED_STAGES
+#define B200RL_FUSED_STAGES 3
+#endif
+constexpr int kFusedWarps = B200RL_FUSED_WARPS, kFusedStages = B200RL_FUSED_STAGES;
+
+template <int WARPS, int STAGES>
+struct FusedSmem {
+  static constexpr int kData = WARPS * STAGES * kChunkBytes;
+  static constexpr int kBarOff = kData;
+  static constexpr int kPartOff = kBarOff + WARPS * STAGES * 8;   // [2][5][WARPS] float
+  static constexpr int kTokOff = kPartOff + 2 * 5 * WARPS * 4;    // [2][8] float: xy,prox,old,adv,mask
+  static constexpr int kBwdOff = kTokOff + 2 * 8 * 4;             // [2][4]: nlse2, A0, lab_add, lvec*8+lsub
+  static constexpr int kSyncOff = kBwdOff + 2 * 4 * 4;            // cnt[2], ready[2] int
+  static constexpr int kSumOff = (kSyncOff + 4 * 4 + 7) & ~7;     // double sum, double count
+  static constexpr int kBytes = kSumOff + 16;
+};
+static_assert(FusedSmem<kFusedWarps, kFusedStages>::kBytes <= 227 * 1024, "fused ring exceeds shared memory");
+
+struct FusedParams {
+  const void* logits;
+  int64_t ld;
+  const int64_t* labels;
+  int T, V;
+  float scale, inv_temp;
+  const float *prox, *old, *adv;
+  const uint8_t* mask;
+  float clip_lo, clip_hi, c_clip, cap;
+  const float* denom;     // N = max(count(mask), 1), device
+  const float* upstream;  // loss scale known in advance, device, may be null (= 1)
+  float *logp, *ent, *lse, *rowmax, *rowmin;
+  float *s_loss, *s_iw, *s_kl;
+  uint8_t *s_clip, *s_dual;
+  float *s_bw, *s_bkl;
+  uint8_t* s_bm;
+  void* dlogits;
+  int64_t ld_out;
+  double* partial;        // [grid][2]
+  unsigned int* counter;
+  float* loss;            // sum(mask * pg * w) / N  (not multiplied by upstream)
+};
+
+__global__ void __launch_bounds__(1024)
+mask_count_kernel(const uint8_t* __restrict__ mask, int64_t T, float* __restrict__ denom) {
+  __shared__ int red[32];
+  int c = 0;
+  for (int64_t i = threadIdx.x; i < T; i += 1024) c += mask[i] != 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < 32; w++) t += red[w];
+    denom[0] = t > 0 ? (float)t : 1.f;  // `count_nonzero() or 1` (functional.py:143)
+  }
+}
+
+template <int DT, int WARPS, int STAGES, bool MINMAX>
+__global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  using L = FusedSmem<WARPS, STAGES>;
+  using E = Elem<DT>;
+  constexpr uint32_t kNeutral = E::kNeutralWord;
+  constexpr bool ENT = true;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* part = reinterpret_cast<float*>(smem + L::kPartOff);
+  float* tok = reinterpret_cast<float*>(smem + L::kTokOff);
+  float* bwdc = reinterpret_cast<float*>(smem + L::kBwdOff);
+  int* cnt = reinterpret_cast<int*>(smem + L::kSyncOff);
+  volatile int* ready = cnt + 2;
+  double* cta_acc = reinterpret_cast<double*>(smem + L::kSumOff);
+  if (threadIdx.x < 4) cnt[threadIdx.x] = 0;
+  if (threadIdx.x == 0) {
+    cta_acc[0] = 0.0;
+    cta_acc[1] = 0.0;
+  }
+  __syncthreads();
+
+  const int T = p.T, V = p.V;
+  const float scale = p.scale;
+  const float up_over_n = (p.upstream ? p.upstream[0] : 1.f) / p.denom[0];
+  const int nrows = (T - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  WarpStream<WARPS, STAGES, 2> ws;
+  ws.init(p.logits, p.ld * E::kBytes, V / E::kPerVec, nrows, smem + warp * STAGES * kChunkBytes,
+          reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
+
+  for (int it = 0; it < nrows; ++it) {
+    const int row = blockIdx.x + it * gridDim.x;
+    const int slot = it & 1, use = it >> 1;
+    // one (rotating) warp fetches the token's scalars early
+    const bool fetch = (it % WARPS) == warp && lane == 0;
+    float xy = 0.f, t_prox = 0.f, t_old = 0.f, t_adv = 0.f, t_mask = 0.f;
+    int t_lab = -1;
+    if (fetch) {
+      const int64_t lab = p.labels[row];
+      const bool ok = lab >= 0 && lab < V;
+      xy = ok ? E::load1(p.logits, (int64_t)row * p.ld + lab) : __int_as_float(0x7fc00000);
+      t_lab = ok ? (int)lab : -1;
+      t_prox = p.prox[row];
+      t_old = p.old[row];
+      t_adv = p.adv[row];
+      t_mask = p.mask[row] ? 1.f : 0.f;
+    }
+
+    // ---------------- pass 1: forward statistics (row from HBM) ----------------
+    LaneState<E> S{kSentinel, 0.f, 0.f, 0.f, 0.f, E::max_init(), E::min_init()};
+    int left = ws.seg_len;
+    while (left > 0) {
+      const int nv = min(kChunkVec, left);
+      left -= nv;
+      const uint32_t base = ws.wait() + lane * 16;
+      if (nv == kChunkVec) {
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
+        ws.release(lane);
+        typename E::MaxT cm = E::vmax(v[0]);
+#pragma unroll
+        for (int i = 1; i < 8; i++) cm = E::cmax(cm, E::vmax(v[i]));
+        S.pmx = E::cmax(S.pmx, cm);
+        if (MINMAX) {
+#pragma unroll
+          for (int i = 0; i < 8; i++) S.pmn = E::cmin(S.pmn, E::vmin(v[i]));
+        }
+        lazy_rescale<E, ENT>(S, cm, scale);
+#pragma unroll
+        for (int i = 0; i < 8; i++) accumulate_vec<E, ENT>(S, v[i], scale);
+      } else {
+        const int nr = (nv + 31) >> 5;
+#pragma unroll 1
+        for (int r = 0; r < nr; r++) {
+          const bool act = r * 32 + lane < nv;
+          uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
+          if (act) v = lds128(base + r * 512);
+          const typename E::MaxT cm = E::vmax(v);
+          S.pmx = E::cmax(S.pmx, cm);
+          if (MINMAX && act) S.pmn = E::cmin(S.pmn, E::vmin(v));
+          lazy_rescale<E, ENT>(S, cm, scale);
+          accumulate_vec<E, ENT>(S, v, scale);
+        }
+        ws.release(lane);
+      }
+    }
+    {
+      const float m = -S.negm;
+      const float s = S.s0 + S.s1, t = S.t0 + S.t1;
+      const float M = warp_max(m);
+      const float dl = m - M;
+      const float f = ex2_approx(dl);
+      const float Ssum = warp_sum(s * f);
+      const float Tt = warp_sum(f * fmaf(dl, s, t));
+      float mx = 0.f, mn = 0.f;
+      if (MINMAX) {
+        mx = warp_max(E::max_f(S.pmx));
+        mn = warp_min(E::min_f(S.pmn));
+      }
+      float* q = part + slot * 5 * WARPS;
+      int old = 0;
+      if (lane == 0) {
+        q[0 * WARPS + warp] = M;
+        q[1 * WARPS + warp] = Ssum;
+        q[2 * WARPS + warp] = Tt;
+        q[3 * WARPS + warp] = mx;
+        q[4 * WARPS + warp] = mn;
+        if (fetch) {
+          float* tk = tok + slot * 8;
+          tk[0] = xy;
+          tk[1] = t_prox;
+          tk[2] = t_old;
+          tk[3] = t_adv;
+          tk[4] = t_mask;
+          tk[5] = __int_as_float(t_lab);
+        }
+        __threadfence_block();
+        old = atomicAdd(&cnt[slot], 1);
+      }
+      old = __shfl_sync(0xffffffffu, old, 0);
+      if (old == WARPS - 1) {
+        // ---- last warp to arrive: row statistics, the token's loss, the backward constants ----
+        __threadfence_block();
+        const volatile float* vq = q;
+        const bool has = lane < WARPS;
+        const float Mw = has ? vq[0 * WARPS + lane] : -kSentinel;
+        const float Sw = has ? vq[1 * WARPS + lane] : 0.f;
+        const float Tw = has ? vq[2 * WARPS + lane] : 0.f;
+        const float mxw = has ? vq[3 * WARPS + lane] : -INFINITY;
+        const float mnw = has ? vq[4 * WARPS + lane] : INFINITY;
+        const float Mr = warp_max(Mw);
+        const float dr = Mw - Mr;
+        const float fr = ex2_approx(dr);
+        const float Sr = warp_sum(Sw * fr);
+        const float Tr = warp_sum(fr * fmaf(dr, Sw, Tw));
+        float mxr = 0.f, mnr = 0.f;
+        if (MINMAX) {
+          mxr = warp_max(mxw);
+          mnr = warp_min(mnw);
+        }
+        if (lane == 0) {
+          cnt[slot] = 0;
+          const volatile float* tk = tok + slot * 8;
+          const float xyr = tk[0], px = tk[1], ol = tk[2], A = tk[3];
+          const bool m = tk[4] != 0.f;
+          const int lab = __float_as_int(tk[5]);
+          const float l2s = log2f(Sr);
+          const float lse_nat = (Mr + l2s) * kLn2;
+          const float lpv = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
+          p.lse[row] = lse_nat;
+          p.logp[row] = lpv;
+          if (p.ent) p.ent[row] = kLn2 * (l2s - Tr / Sr);
+          if (MINMAX) {
+            if (p.rowmax) p.rowmax[row] = mxr;
+            if (p.rowmin) p.rowmin[row] = mnr;
+          }
+          const PpoToken k = ppo_token(lpv, px, ol, A, m, p.clip_lo, p.clip_hi, p.c_clip, p.cap);
+          if (p.s_loss) p.s_loss[row] = k.pgw;
+          if (p.s_iw) p.s_iw[row] = k.ratio;
+          if (p.s_kl) p.s_kl[row] = k.kl;
+          if (p.s_clip) p.s_clip[row] = k.clip;
+          if (p.s_dual) p.s_dual[row] = k.dual;
+          if (p.s_bw) p.s_bw[row] = k.w;
+          if (p.s_bkl) p.s_bkl[row] = k.bkl;
+          if (p.s_bm) p.s_bm[row] = k.bmask;
+          if (m) {  // rows of a CTA are finalised strictly in order: a deterministic sum
+            cta_acc[0] += (double)k.pgw;
+            cta_acc[1] += 1.0;
+          }
+          // same operation order as ppo_loss_bwd_kernel + logprob_bwd_kernel (bit-identical dlogits)
+          const float glp = k.dlogp * up_over_n;
+          float* bc = bwdc + slot * 4;
+          bc[0] = -lse_nat * kLog2e;
+          bc[1] = -glp * p.inv_temp;
+          bc[2] = glp * p.inv_temp;
+          bc[3] = __int_as_float(lab);
+          __threadfence_block();
+          ready[slot] = use + 1;
+        }
+      }
+    }
+
+    // ---------------- pass 2: backward (row again, from L2) ----------------
+    if (lane == 0) {
+      while (ready[slot] < use + 1) {
+      }
+    }
+    __syncwarp();
+    __threadfence_block();
+    const volatile float* bc = bwdc + slot * 4;
+    const float nlse2 = bc[0], A0 = bc[1], lab_add = bc[2];
+    const int lab = __float_as_int(bc[3]);
+    const int lvec = lab >= 0 ? lab / E::kPerVec : -1;
+    const int lsub = lab >= 0 ? lab % E::kPerVec : 0;
+    char* out_row = reinterpret_cast<char*>(p.dlogits) + ((int64_t)row * p.ld_out) * E::kBytes;
+    left = ws.seg_len;
+    int v0 = ws.sv + lane;
+    while (left > 0) {
+      const int nv = min(kChunkVec, left);
+      left -= nv;
+      const uint32_t base = ws.wait() + lane * 16;
+      if (nv == kChunkVec) {
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
+        ws.release(lane);
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+          bwd_vec<E, false>(v[i], v0 + i * 32, true, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
+      } else {
+        const int nr = (nv + 31) >> 5;
+#pragma unroll 1
+        for (int r = 0; r < nr; r++) {
+          const bool act = r * 32 + lane < nv;
+          uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
+          if (act) v = lds128(base + r * 512);
+          bwd_vec<E, false>(v, v0 + r * 32, act, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
+        }
+        ws.release(lane);
+      }
+      v0 += kChunkVec;
+    }
+  }
+
+  // ---- loss: per-CTA partial, the last CTA adds them in index order --------------------------
+  __syncthreads();
+  __shared__ bool is_last;
+  if (threadIdx.x == 0) {
+    p.partial[2 * blockIdx.x] = cta_acc[0];
+    p.partial[2 * blockIdx.x + 1] = cta_acc[1];
+    __threadfence();
+    is_last = atomicAdd(p.counter, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (is_last && threadIdx.x == 0) {
+    __threadfence();
+    const volatile double* part_g = p.partial;
+    double s = 0.0;
+    for (unsigned b = 0; b < gridDim.x; b++) s += part_g[2 * b];
+    p.loss[0] = (float)s / p.denom[0];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+scale_inplace_kernel(uint4* __restrict__ buf, int64_t nvec, int dtype, const float* __restrict__ g) {
+  const float s = g[0];
+  if (s == 1.f) return;  // the common case: nothing is read or written
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * 256) {
+    uint4 v = buf[i];
+    if (dtype == B200RL_FP32) {
+      float x[4];
+      Elem<B200RL_FP32>::unpack(v, x);
+#pragma unroll
+      for (int j = 0; j < 4; j++) x[j] *= s;
+      buf[i] = Elem<B200RL_FP32>::pack(x);
+    } else if (dtype == B200RL_BF16) {
+      float x[8];
+      Elem<B200RL_BF16>::unpack(v, x);
+#pragma unroll
+      for (int j = 0; j < 8; j++) x[j] *= s;
+      buf[i] = Elem<B200RL_BF16>::pack(x);
+    } else {
+      float x[8];
+      Elem<B200RL_FP16>::unpack(v, x);
+#pragma unroll
+      for (int j = 0; j < 8; j++) x[j] *= s;
+      buf[i] = Elem<B200RL_FP16>::pack(x);
+    }
+  }
+}
+
+struct FusedWs {
+  unsigned int* counter;
+  double* partial;
+  size_t bytes;
+};
+FusedWs fused_ws(void* ws) {
+  FusedWs W;
+  W.counter = (unsigned int*)ws;
+  W.partial = (double*)((char*)ws + 256);
+  W.bytes = 256 + 2 * sizeof(double) * 1024;  // up to 1024 CTAs
+  return W;
+}
+
+template <typename K>
+int set_smem_once(K kernel, int bytes) {
+  static const void* seen_fn[32];
+  static int seen_dev[32];
+  static int n_seen = 0;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const void* fn = reinterpret_cast<const void*>(kernel);
+  for (int i = 0; i < n_seen && i < 32; i++)
+    if (seen_fn[i] == fn && seen_dev[i] == dev) return 0;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) {
+    set_last_error("cudaFuncSetAttribute(smem=%d): %s", bytes, cudaGetErrorString(e));
+    return (int)e;
+  }
+  if (n_seen < 32) {
+    seen_fn[n_seen] = fn;
+    seen_dev[n_seen] = dev;
+    n_seen++;
+  }
+  return 0;
+}
+
+template <int DT, bool MINMAX>
+int launch_fused(const FusedParams& p, cudaStream_t st) {
+  auto k = grpo_fused_kernel<DT, kFusedWarps, kFusedStages, MINMAX>;
+  constexpr int smem = FusedSmem<kFusedWarps, kFusedStages>::kBytes;
+  int rc = set_smem_once(k, smem);
+  if (rc) return rc;
+  const int grid = min(p.T, min(sm_count(), 1024));
+  k<<<grid, kFusedWarps * 32, smem, st>>>(p);
+  return check_launch("grpo_fused_kernel");
+}
+
+}  // namespace
+}  // namespace b200rl
+
+extern "C" {
+
+size_t b200rl_grpo_fused_workspace_bytes(int64_t T) {
+  (void)T;
+  return b200rl::fused_ws(nullptr).bytes;
+}
+
+int b200rl_grpo_fused_step(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                           int64_t T, int64_t V, float temperature, const float* prox_logp,
+                           const float* old_logp, const float* adv, const uint8_t* mask,
+                           float clip_lo, float clip_hi, float c_clip, float cap,
+                           const float* upstream, float* logp, float* entropy, float* lse,
+                           float* rowmax, float* rowmin, float* stat_loss, float* stat_imp_weight,
+                           float* stat_approx_kl, uint8_t* stat_clip_mask,
+                           uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
+                           float* stat_behave_approx_kl, uint8_t* stat_behave_mask, void* dlogits,
+                           int64_t ld_out, float* loss, float* denom, void* workspace,
+                           size_t workspace_bytes, void* stream) {
+  using namespace b200rl;
+  B200RL_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
+  B200RL_REQUIRE(ld >= V && ld_out >= V, "row stride < V");
+  B200RL_REQUIRE(temperature > 0.f, "temperature must be > 0, got %f", temperature);
+  B200RL_REQUIRE(T < INT32_MAX && V < INT32_MAX, "T and V must fit int32");
+  B200RL_REQUIRE(loss && denom && workspace, "loss/denom/workspace must not be null");
+  B200RL_REQUIRE(!(c_clip > 0.f) || c_clip > 1.f, "c_clip must be > 1 (functional.py:157), got %f", c_clip);
+  B200RL_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "workspace must be 256-B aligned");
+  FusedWs W = fused_ws(workspace);
+  if (workspace_bytes < W.bytes) {
+    set_last_error("fused workspace too small: %zu < %zu", workspace_bytes, W.bytes);
+    return B200RL_EWORKSPACE;
+  }
+  B200RL_REQUIRE(dtype == B200RL_BF16 || dtype == B200RL_FP16 || dtype == B200RL_FP32,
+                 "unsupported logits dtype code %d", dtype);
+  const int pv = dtype == B200RL_FP32 ? 4 : 8;
+  const bool fast = (V % pv == 0) && (ld % pv == 0) && (ld_out % pv == 0) &&
+                    (reinterpret_cast<uintptr_t>(logits) % 16 == 0) &&
+                    (reinterpret_cast<uintptr_t>(dlogits) % 16 == 0);
+  if (!fast) {
+    set_last_error("fused step needs 16-byte aligned rows (V %% %d == 0); use the separate fwd/bwd entry points", pv);
+    return B200RL_EUNSUPPORTED;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200RL_CUDA(cudaMemsetAsync(workspace, 0, 256, st));
+  if (T == 0) {
+    B200RL_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), st));
+    return B200RL_OK;
+  }
+  B200RL_REQUIRE(logits && labels && prox_logp && old_logp && adv && mask && logp && lse && dlogits,
+                 "null pointer");
+  mask_count_kernel<<<1, 1024, 0, st>>>(mask, T, denom);
+  FusedParams p;
+  p.logits = logits; p.ld = ld; p.labels = labels; p.T = (int)T; p.V = (int)V;
+  p.scale = (float)(1.4426950408889634 / (double)temperature);
+  p.inv_temp = (float)(1.0 / (double)temperature);
+  p.prox = prox_logp; p.old = old_logp; p.adv = adv; p.mask = mask;
+  p.clip_lo = clip_lo; p.clip_hi = clip_hi; p.c_clip = c_clip; p.cap = cap;
+  p.denom = denom; p.upstream = upstream;
+  p.logp = logp; p.ent = entropy; p.lse = lse; p.rowmax = rowmax; p.rowmin = rowmin;
+  p.s_loss = stat_loss; p.s_iw = stat_imp_weight; p.s_kl = stat_approx_kl;
+  p.s_clip = stat_clip_mask; p.s_dual = stat_dual_clip_mask;
+  p.s_bw = stat_behave_imp_weight; p.s_bkl = stat_behave_approx_kl; p.s_bm = stat_behave_mask;
+  p.dlogits = dlogits; p.ld_out = ld_out;
+  p.partial = W.partial; p.counter = W.counter; p.loss = loss;
+  const bool mm = rowmax != nullptr || rowmin != nullptr;
+  switch (dtype) {
+    case B200RL_BF16: return mm ? launch_fused<B200RL_BF16, true>(p, st) : launch_fused<B200RL_BF16, false>(p, st);
+    case B200RL_FP16: return mm ? launch_fused<B200RL_FP16, true>(p, st) : launch_fused<B200RL_FP16, false>(p, st);
+    default: return mm ? launch_fused<B200RL_FP32, true>(p, st) : launch_fused<B200RL_FP32, false>(p, st);
+  }
+}
+
+int b200rl_scale_inplace(void* buf, int dtype, int64_t numel, const float* scale, void* stream) {
+  using namespace b200rl;
+  B200RL_REQUIRE(numel >= 0, "negative numel");
+  if (numel == 0) return B200RL_OK;
+  B200RL_REQUIRE(buf && scale, "null pointer");
+  B200RL_REQUIRE(dtype == B200RL_BF16 || dtype == B200RL_FP16 || dtype == B200RL_FP32,
+                 "unsupported dtype code %d", dtype);
+  const int pv = dtype == B200RL_FP32 ? 4 : 8;
+  B200RL_REQUIRE(numel % pv == 0 && (reinterpret_cast<uintptr_t>(buf) & 15) == 0,
+                 "buffer must be 16-byte aligned and a whole number of 16-byte vectors");
+  const int64_t nvec = numel / pv;
+  int64_t blocks = (nvec + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  scale_inplace_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((uint4*)buf, nvec, dtype, scale);
+  return check_launch("scale_inplace_kernel");
+}
+
+}  // extern "C"

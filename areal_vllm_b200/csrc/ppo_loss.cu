@@ -10,6 +10,7 @@
 // Reduction: per-CTA partial sums (fp64) -> workspace -> the last CTA to finish adds them in
 // index order. Fixed order => deterministic loss for a given T.
 #include "common.cuh"
+#include "ppo_math.cuh"
 
 namespace b200rl {
 namespace {
@@ -38,14 +39,6 @@ LossWs loss_ws(void* ws, int64_t T) {
   return W;
 }
 
-// torch.maximum / minimum / clamp propagate NaN; fmaxf/fminf do not.
-__device__ __forceinline__ float tmax(float a, float b) {
-  return (a != a || b != b) ? __int_as_float(0x7fc00000) : fmaxf(a, b);
-}
-__device__ __forceinline__ float tmin(float a, float b) {
-  return (a != a || b != b) ? __int_as_float(0x7fc00000) : fminf(a, b);
-}
-
 struct Params {
   const float *logp, *prox, *old, *adv;
   const uint8_t* mask;
@@ -67,9 +60,6 @@ __global__ void __launch_bounds__(kThreads) ppo_loss_fwd_kernel(const Params p) 
   __shared__ double red[2][kThreads / 32];
   __shared__ bool is_last;
   const int tid = threadIdx.x;
-  const bool has_c = p.c_clip > 0.f;
-  const bool has_cap = p.cap >= 0.f;
-  const bool no_bw = p.cap < -1.5f;
   const bool norm = p.adv_mean != nullptr || p.adv_denom != nullptr;
   float tsum = 0.f;
   int tcnt = 0;
@@ -88,49 +78,21 @@ __global__ void __launch_bounds__(kThreads) ppo_loss_fwd_kernel(const Params p) 
         A = (float)(((double)A * (m ? 1.0 : 0.0) - mu) / dn);
         if (p.adv_out) p.adv_out[t] = A;
       }
-      // functional.py:144
-      const float d = lp - px;
-      const float r = m ? expf(d) : 0.f;
-      // functional.py:146-150  clamp(r, lo, hi) = min(max(r, lo), hi)
-      const float rc = tmin(tmax(r, p.clip_lo), p.clip_hi);
-      // functional.py:152-155
-      const float nA = -A;
-      const float l1 = nA * r, l2 = nA * rc;
-      const bool clip = (l1 < l2) && m;
-      float pg = tmax(l1, l2);
-      // gradient wrt logp through max/clamp (ties split 1/2, clamp passes on inclusive bounds)
-      const float dl1 = m ? l1 : 0.f;  // d l1 / d lp = -A * r
-      const float dl2 = (r >= p.clip_lo && r <= p.clip_hi) ? dl1 : 0.f;
-      float gp = (l1 > l2) ? dl1 : ((l1 < l2) ? dl2 : 0.5f * (dl1 + dl2));
-      bool dual = false;
-      if (has_c) {  // functional.py:156-160
-        const float sg = (A > 0.f) ? 1.f : ((A < 0.f) ? -1.f : ((A == 0.f) ? 0.f : A));
-        const float l3 = (sg * p.c_clip) * A;
-        dual = (l3 < pg) && m;
-        gp = (pg < l3) ? gp : ((pg == l3) ? 0.5f * gp : 0.f);
-        pg = tmin(pg, l3);
-      }
-      // functional.py:163-172
-      float bk = px - ol;
-      float w = expf(bk);
-      const bool bm = has_cap ? ((w <= p.cap) && m) : m;
-      bk = bm ? bk : 0.f;
-      w = bm ? w : 0.f;
-      if (no_bw) w = 1.f;  // legacy actor_loss_fn without proximal_logprobs: no weighting at all
-      const float pgw = pg * w;
+      const PpoToken tk = ppo_token(lp, px, ol, A, m, p.clip_lo, p.clip_hi, p.c_clip, p.cap);
+      const float pgw = tk.pgw;
       if (m) {
         tsum += pgw;
         tcnt += 1;
       }
       if (p.s_loss) p.s_loss[t] = pgw;
-      if (p.s_iw) p.s_iw[t] = r;
-      if (p.s_kl) p.s_kl[t] = d;
-      if (p.s_clip) p.s_clip[t] = clip;
-      if (p.s_dual) p.s_dual[t] = dual;
-      if (p.s_bw) p.s_bw[t] = w;
-      if (p.s_bkl) p.s_bkl[t] = bk;
-      if (p.s_bm) p.s_bm[t] = bm;
-      if (p.dlogp) p.dlogp[t] = m ? gp * w : 0.f;
+      if (p.s_iw) p.s_iw[t] = tk.ratio;
+      if (p.s_kl) p.s_kl[t] = tk.kl;
+      if (p.s_clip) p.s_clip[t] = tk.clip;
+      if (p.s_dual) p.s_dual[t] = tk.dual;
+      if (p.s_bw) p.s_bw[t] = tk.w;
+      if (p.s_bkl) p.s_bkl[t] = tk.bkl;
+      if (p.s_bm) p.s_bm[t] = tk.bmask;
+      if (p.dlogp) p.dlogp[t] = tk.dlogp;
     }
   }
   // block reduce (fp64)

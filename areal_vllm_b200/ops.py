@@ -191,6 +191,90 @@ def logprob_entropy_bwd(logits, labels, lse, entropy, g_logp, g_ent, temperature
 
 
 # --------------------------------------------------------------------------------------------
+# H1+H2 fused GRPO step (eager only: it allocates and fills dlogits in the forward)
+# --------------------------------------------------------------------------------------------
+def _raw_grpo_fused_step(
+    logits: Tensor, labels: Tensor, prox_logp: Tensor, old_logp: Tensor, adv: Tensor, mask: Tensor,
+    temperature: float, clip_lo: float, clip_hi: float, c_clip: float, cap: float,
+    upstream: Optional[Tensor], need_minmax: bool,
+):
+    """-> dict of outputs, or None when the kernel does not support the layout (unaligned rows)."""
+    _check_logits(logits, labels)
+    T, V = logits.shape
+    dev = logits.device
+    pv = 4 if logits.dtype == torch.float32 else 8
+    if V % pv or logits.stride(0) % pv or logits.data_ptr() % 16:
+        return None
+    f32 = dict(dtype=torch.float32, device=dev)
+    u8 = dict(dtype=torch.uint8, device=dev)
+
+    def tokvec(t: Tensor, name: str) -> Tensor:
+        if t.shape != (T,):
+            raise RuntimeError(f"{name} must have shape ({T},), got {tuple(t.shape)}")
+        return t.detach().to(torch.float32).contiguous()
+
+    px, ol, ad = tokvec(prox_logp, "prox_logp"), tokvec(old_logp, "logprobs"), tokvec(adv, "advantages")
+    if mask.shape != (T,):
+        raise RuntimeError(f"loss_mask must have shape ({T},)")
+    mk = (mask if mask.dtype == torch.bool else mask != 0).contiguous().view(torch.uint8)
+    up = None if upstream is None else upstream.detach().to(torch.float32).reshape(1).contiguous()
+    o = dict(
+        logp=torch.empty(T, **f32), entropy=torch.empty(T, **f32), lse=torch.empty(T, **f32),
+        rowmax=torch.empty(T if need_minmax else 0, **f32), rowmin=torch.empty(T if need_minmax else 0, **f32),
+        s_loss=torch.empty(T, **f32), s_iw=torch.empty(T, **f32), s_kl=torch.empty(T, **f32),
+        s_clip=torch.empty(T, **u8), s_dual=torch.empty(T, **u8), s_bw=torch.empty(T, **f32),
+        s_bkl=torch.empty(T, **f32), s_bm=torch.empty(T, **u8),
+        dlogits=torch.empty((T, V), dtype=logits.dtype, device=dev),
+        loss=torch.empty((), **f32), denom=torch.empty(1, **f32),
+    )
+    ws = _lib.workspace(lib.b200rl_grpo_fused_workspace_bytes(T), dev)
+    with _on(dev):
+        rc = lib.b200rl_grpo_fused_step(
+            ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
+            ptr(labels), T, V, float(temperature), ptr(px), ptr(ol), ptr(ad), ptr(mk),
+            float(clip_lo), float(clip_hi), float(c_clip), float(cap), ptr(up),
+            ptr(o["logp"]), ptr(o["entropy"]), ptr(o["lse"]),
+            ptr(o["rowmax"]) if need_minmax else None, ptr(o["rowmin"]) if need_minmax else None,
+            ptr(o["s_loss"]), ptr(o["s_iw"]), ptr(o["s_kl"]), ptr(o["s_clip"]), ptr(o["s_dual"]),
+            ptr(o["s_bw"]), ptr(o["s_bkl"]), ptr(o["s_bm"]), ptr(o["dlogits"]), V,
+            ptr(o["loss"]), ptr(o["denom"]), ptr(ws), ws.numel(), stream_handle(dev),
+        )
+    if rc == -2:  # B200RL_EUNSUPPORTED
+        return None
+    check(rc, "b200rl_grpo_fused_step")
+    return o
+
+
+def scale_inplace_(buf: Tensor, scale: Tensor) -> Tensor:
+    """buf *= scale (device scalar); launches a kernel that exits at once when scale == 1."""
+    _lib.require_cuda(buf=buf, scale=scale)
+    _lib.require_contiguous(buf=buf)
+    dev = buf.device
+    sc = scale.detach().to(torch.float32).reshape(1).contiguous()
+    with _on(dev):
+        rc = lib.b200rl_scale_inplace(ptr(buf), _lib.DTYPE_CODE[buf.dtype], buf.numel(), ptr(sc), stream_handle(dev))
+    check(rc, "b200rl_scale_inplace")
+    return buf
+
+
+class _GrpoFusedFn(torch.autograd.Function):
+    """loss = upstream * PPO loss; the gradient w.r.t. logits was already written by the forward."""
+
+    @staticmethod
+    def forward(ctx, logits, loss_unscaled, dlogits, upstream):
+        ctx.save_for_backward(dlogits)
+        ctx.set_materialize_grads(False)
+        return loss_unscaled * upstream.reshape(()) if upstream is not None else loss_unscaled.clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        (dlogits,) = ctx.saved_tensors
+        if g is None:
+            return None, None, None, None
+        return scale_inplace_(dlogits, g), None, None, None
+
+
+# --------------------------------------------------------------------------------------------
 # H3 GAE
 # --------------------------------------------------------------------------------------------
 def _raw_gae_1d_nolp_misalign(

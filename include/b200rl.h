@@ -62,6 +62,38 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
                                void* dlogits, int64_t ld_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * H1+H2 fused: the whole GRPO actor step on one packed micro-batch in ONE pass over HBM.
+ * ref: areal/engine/ppo/actor.py:292-367 (grpo_loss_fn) followed by loss.backward()
+ *      (areal/engine/fsdp_engine.py:542-550).
+ *
+ * Computes everything b200rl_logprob_entropy_fwd (with entropy and row max/min) and
+ * b200rl_ppo_loss_fwd compute, and also dlogits = d(upstream * loss)/d logits, with 4*V instead of
+ * 6*V bytes of HBM traffic per token: each row is read once from HBM for the forward statistics
+ * and a second time, immediately, out of L2 for the backward. Entropy is treated as detached (it
+ * is in grpo_loss_fn, actor.py:312). `upstream` (DEVICE scalar, NULL = 1) is the factor the
+ * caller will multiply the loss by before backward(); the engine's `loss_scale` does not depend on
+ * the loss (fsdp_engine.py:543-547), so it is known here. `loss[0]` is NOT multiplied by it.
+ * `denom[0]` receives N = max(count(mask), 1). Same dtypes/flags as the separate entry points;
+ * returns B200RL_EUNSUPPORTED when rows are not 16-byte aligned (use the separate calls then).
+ * b200rl_scale_inplace multiplies a gradient buffer by a DEVICE scalar and does nothing (no
+ * memory traffic) when that scalar is exactly 1: the autograd backward of the fused step uses it
+ * to stay correct for any incoming gradient.
+ */
+size_t b200rl_grpo_fused_workspace_bytes(int64_t T);
+int b200rl_grpo_fused_step(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                           int64_t T, int64_t V, float temperature, const float* prox_logp,
+                           const float* old_logp, const float* adv, const uint8_t* mask,
+                           float clip_lo, float clip_hi, float c_clip, float cap,
+                           const float* upstream, float* logp, float* entropy, float* lse,
+                           float* rowmax, float* rowmin, float* stat_loss, float* stat_imp_weight,
+                           float* stat_approx_kl, uint8_t* stat_clip_mask,
+                           uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
+                           float* stat_behave_approx_kl, uint8_t* stat_behave_mask, void* dlogits,
+                           int64_t ld_out, float* loss, float* denom, void* workspace,
+                           size_t workspace_bytes, void* stream);
+int b200rl_scale_inplace(void* buf, int dtype, int64_t numel, const float* scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * H3  GAE over packed variable-length sequences ("1d, no-overlap, misaligned").
  * ref: csrc/cugae/gae.cu:10-60 (gae_kernel_1d_nolp_misalign + launcher),
  *      realhf/impl/model/utils/ppo_functional.py:292-366 (pygae1d_nolp_misalign, cugae1d_nolp_misalign_func).

@@ -65,3 +65,21 @@ def f32(x):
     out = pkg.ops.logprob_entropy_fwd(x, y32, 1.0, True, False); lse, ent = out[2], out[1]
 bench32("fp32 fwd (+entropy)", f32, 4.0 * T32 * V)
 bench32("fp32 bwd", lambda x: pkg.ops.logprob_entropy_bwd(x, y32, lse, ent, g32, None, 1.0), 8.0 * T32 * V)
+
+# fused GRPO step: 4*V bytes of HBM traffic per token (bf16)
+from areal_vllm_b200.actor import grpo_loss_fn_fused, grpo_loss_fn
+Tm = 10240
+data = dict(input_ids=y[:Tm], logprobs=-torch.rand(Tm, device=dev) * 4, advantages=torch.randn(Tm, device=dev),
+            loss_mask=(torch.rand(Tm, device=dev) < 0.7).float(), prox_logp=-torch.rand(Tm, device=dev) * 4)
+ls = torch.tensor(0.5, device=dev)
+def fused(x):
+    xg = x[:Tm].detach().requires_grad_(True)
+    loss = grpo_loss_fn_fused(xg, data, 1.0, 0.4, None, None, 5.0, loss_scale=ls)
+    torch.autograd.grad(loss, xg)
+def separate(x):
+    xg = x[:Tm].detach().requires_grad_(True)
+    loss = grpo_loss_fn(xg, data, 1.0, 0.4, None, None, 5.0)
+    torch.autograd.grad(loss * ls, xg)
+bench("separate fwd+loss+bwd (6V)", separate, 6.0 * Tm * V)
+bench("FUSED step (bytes=4V)", fused, 4.0 * Tm * V)
+bench("FUSED step (as 6V-equiv)", fused, 6.0 * Tm * V)
