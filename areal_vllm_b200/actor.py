@@ -310,7 +310,7 @@ def grpo_loss_fn_fused(
             logits.detach(), labels, prox_logp, old_logp, advantages, loss_mask, float(temperature),
             1.0 - eps_clip, 1.0 + (eps_clip if eps_clip_higher is None else eps_clip_higher),
             -1.0 if c_clip is None else float(c_clip),
-            -1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap), up, want_stats)
+            -1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap), up, True)
     if out is None:
         loss = grpo_loss_fn(logits, input_data, temperature, eps_clip, eps_clip_higher, c_clip,
                             behav_imp_weight_cap, stats=stats)

@@ -25,10 +25,10 @@ namespace {
 using namespace lp;
 
 #ifndef B200RL_FUSED_WARPS
-#define B200RL_FUSED_WARPS 16
+#define B200RL_FUSED_WARPS 24
 #endif
 #ifndef B200RL_FUSED_STAGES
-#define B200RL_FUSED_STAGES 3
+#define B200RL_FUSED_STAGES 2
 #endif
 constexpr int kFusedWarps = B200RL_FUSED_WARPS, kFusedStages = B200RL_FUSED_STAGES;
 

@@ -302,7 +302,7 @@ def main_b200rl(args):
 
     import areal_vllm_b200 as pkg
     from areal_vllm_b200 import ops
-    from areal_vllm_b200.actor import AdvNorm, grpo_loss_fn
+    from areal_vllm_b200.actor import AdvNorm, grpo_loss_fn, grpo_loss_fn_fused
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -351,6 +351,22 @@ def main_b200rl(args):
 
     bwd_events = []
     fwd_events = []
+
+    unit_scale = torch.ones((), device=dev)
+
+    def hot_step_fused(step_idx: int):
+        """The same step through the fused extension API (grpo_loss_fn_fused: loss_scale handed
+        in up front, forward + loss + dlogits in one kernel, 4*V bytes of HBM traffic per token)."""
+        adv_norm(adv_pad, pad_mask)
+        total = torch.zeros((), device=dev)
+        for k, mb in enumerate(dev_mbs):
+            T = mb["input_ids"].numel()
+            x = logits_bufs[(k + step_idx) % N_LOGITS_BUFFERS][:T].detach().requires_grad_(True)
+            loss = grpo_loss_fn_fused(x, mb, TEMPERATURE, EPS_CLIP, None, None, CAP, loss_scale=unit_scale)
+            (dlogits,) = torch.autograd.grad(loss, x)
+            total = total + loss.detach()
+            del dlogits
+        return total
 
     def hot_step(step_idx: int, record: bool, src_logits=None):
         """One pass of the hot path over the whole batch; returns the summed loss (device)."""
@@ -438,6 +454,34 @@ def main_b200rl(args):
                 "frac": fwd_bytes / (fwd_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_token": 2 * V},
         "fwd_bwd_frac_of_peak": (fwd_bytes + bwd_bytes) / ((fwd_ms + bwd_ms) * 1e-3) / 1e9 / peak,
     }
+
+    # ---------------- the fused extension path, same step, same buffers ----------------
+    fused = None
+    if not args.no_fused:
+        for w in range(max(args.warmup, 1)):
+            hot_step_fused(w)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for s_ in range(args.steps):
+            hot_step_fused(args.warmup + s_)
+        f1.record()
+        torch.cuda.synchronize()
+        fms = f0.elapsed_time(f1)
+        if world > 1:
+            t = torch.tensor([fms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            fms = float(t.item())
+        fval = total_tok * args.steps / (fms * 1e-3)
+        fused = {"api": "areal_vllm_b200.actor.grpo_loss_fn_fused(..., loss_scale=...) + backward()",
+                 "value": fval, "unit": "tokens/s", "ms_per_step": fms / args.steps,
+                 "speedup_vs_separate_path": fval / value,
+                 "algorithmic_bytes_per_token": 4 * V,
+                 "hbm_GBps_at_4V": fval * 4 * V / 1e9, "frac_of_measured_peak_at_4V": fval * 4 * V / 1e9 / peak,
+                 "note": "each row is read from HBM once (forward statistics) and again from L2 for the "
+                         "backward; needs the loss scale before backward(), see INTEGRATION.md"}
 
     # ---------------- e2e: host buffers, H2D inside the timed region ----------------
     e2e = None
@@ -534,7 +578,7 @@ def main_b200rl(args):
                        "cache": f"inputs larger than L2: {N_LOGITS_BUFFERS} rotating logits buffers of "
                                 f"{max_T}x{V} bf16 = {max_T * V * 2 / 1e9:.2f} GB each"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "clocks": clocks,
-            "extra": extras,
+            "fused_step": fused, "extra": extras,
             "gpu_launches": args.steps * (3 + 4 * n_mb),
             "gpu_launches_note": "per step: masked_moments+moments_finalize+masked_normalize, then per "
                                  "micro-batch logprob_fwd, ppo_loss_fwd, ppo_loss_bwd, logprob_bwd",
@@ -553,6 +597,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the GAE / interval_op side metrics")
+    ap.add_argument("--no-fused", action="store_true", help="skip the fused-step extension measurement")
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)

@@ -24,6 +24,21 @@ if what == "h1":
         d2 = pkg.ops.logprob_entropy_bwd(x, y, lse, ent, g, 0.01 * g, 1.0)
     torch.cuda.synchronize()
     print("ok", float(logp.sum()), float(d.float().abs().sum()))
+elif what == "fused":
+    from areal_vllm_b200.actor import grpo_loss_fn_fused
+    gen = torch.Generator(device=dev).manual_seed(0)
+    x = torch.empty(T, V, dtype=torch.bfloat16, device=dev)
+    for lo in range(0, T, 2048):
+        x[lo:lo + 2048] = (torch.randn(min(2048, T - lo), V, generator=gen, device=dev) * 2).bfloat16()
+    y = torch.randint(0, V, (T,), generator=gen, device=dev)
+    data = dict(input_ids=y, logprobs=-torch.rand(T, device=dev) * 4, advantages=torch.randn(T, device=dev),
+                loss_mask=(torch.rand(T, device=dev) < 0.7).float(), prox_logp=-torch.rand(T, device=dev) * 4)
+    for _ in range(3):
+        xg = x.detach().requires_grad_(True)
+        loss = grpo_loss_fn_fused(xg, data, 1.0, 0.4, None, None, 5.0, loss_scale=torch.tensor(1.0, device=dev))
+        (d,) = torch.autograd.grad(loss, xg)
+    torch.cuda.synchronize()
+    print("ok", float(loss), float(d.float().abs().sum()))
 elif what == "gae":
     rng = np.random.default_rng(0)
     B = 65536

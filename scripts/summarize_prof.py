@@ -75,7 +75,8 @@ def full(rep, out, note):
 if os.path.exists("gpurun_out/launches.csv"):
     launches("gpurun_out/launches.csv", f"{out_dir}/{tag}_launches_bench.txt")
 for name, note in (("prof_h1", "`python scripts/prof_h1.py 2048 h1` (T=2048 rows x V=151936 bf16 = 622 MB per pass)"),
-                   ("prof_gae", "`python scripts/prof_h1.py 0 gae`"),):
+                   ("prof_fused", "`python scripts/prof_h1.py 2048 fused` (fused GRPO step, T=2048 rows x V=151936 bf16; algorithmic HBM bytes 4*V/token = 1244.7 MB)"),
+                   ("prof_gae", "`python scripts/prof_h1.py 0 gae` (65536 sequences of 64-2048 tokens, 69 M tokens)"),):
     rep = f"gpurun_out/{name}.ncu-rep"
     if os.path.exists(rep):
         full(rep, f"{out_dir}/{tag}_ncu_{name[5:]}.txt", note)
