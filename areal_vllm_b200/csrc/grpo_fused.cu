@@ -30,7 +30,14 @@ using namespace lp;
 #ifndef B200RL_FUSED_STAGES
 #define B200RL_FUSED_STAGES 2
 #endif
+// Skewed order (backward of row r after the forward of row r+1) hides the wait for the row's
+// finalisation but keeps two rows per SM live: 90 MB plus the dlogits stream no longer fits the
+// L2 (measured: DRAM reads 1055 MB instead of 626 MB per 2048 rows, 6.8 M instead of 9.5 M tok/s).
+#ifndef B200RL_FUSED_SKEW
+#define B200RL_FUSED_SKEW 0
+#endif
 constexpr int kFusedWarps = B200RL_FUSED_WARPS, kFusedStages = B200RL_FUSED_STAGES;
+constexpr bool kFusedSkew = B200RL_FUSED_SKEW != 0;
 
 template <int WARPS, int STAGES>
 struct FusedSmem {
@@ -84,7 +91,7 @@ mask_count_kernel(const uint8_t* __restrict__ mask, int64_t T, float* __restrict
   }
 }
 
-template <int DT, int WARPS, int STAGES, bool MINMAX>
+template <int DT, int WARPS, int STAGES, bool MINMAX, bool SKEW>
 __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FusedSmem<WARPS, STAGES>;
@@ -109,202 +116,222 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
   const float scale = p.scale;
   const float up_over_n = (p.upstream ? p.upstream[0] : 1.f) / p.denom[0];
   const int nrows = (T - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-  WarpStream<WARPS, STAGES, 2> ws;
+  WarpStream<WARPS, STAGES, 2, SKEW> ws;
   ws.init(p.logits, p.ld * E::kBytes, V / E::kPerVec, nrows, smem + warp * STAGES * kChunkBytes,
           reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
 
-  for (int it = 0; it < nrows; ++it) {
+  // pass 1 of row-iteration `it` (forward statistics + the token's loss, row from HBM)
+  auto pass1 = [&](int it) {
+      const int row = blockIdx.x + it * gridDim.x;
+      const int slot = it & 1, use = it >> 1;
+      // one (rotating) warp fetches the token's scalars early
+      const bool fetch = (it % WARPS) == warp && lane == 0;
+      float xy = 0.f, t_prox = 0.f, t_old = 0.f, t_adv = 0.f, t_mask = 0.f;
+      int t_lab = -1;
+      if (fetch) {
+        const int64_t lab = p.labels[row];
+        const bool ok = lab >= 0 && lab < V;
+        xy = ok ? E::load1(p.logits, (int64_t)row * p.ld + lab) : __int_as_float(0x7fc00000);
+        t_lab = ok ? (int)lab : -1;
+        t_prox = p.prox[row];
+        t_old = p.old[row];
+        t_adv = p.adv[row];
+        t_mask = p.mask[row] ? 1.f : 0.f;
+      }
+
+      // ---------------- pass 1: forward statistics (row from HBM) ----------------
+      LaneState<E> S{kSentinel, 0.f, 0.f, 0.f, 0.f, E::max_init(), E::min_init()};
+      int left = ws.seg_len;
+      while (left > 0) {
+        const int nv = min(kChunkVec, left);
+        left -= nv;
+        const uint32_t base = ws.wait() + lane * 16;
+        if (nv == kChunkVec) {
+          uint4 v[8];
+#pragma unroll
+          for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
+          ws.release(lane);
+          typename E::MaxT cm = E::vmax(v[0]);
+#pragma unroll
+          for (int i = 1; i < 8; i++) cm = E::cmax(cm, E::vmax(v[i]));
+          S.pmx = E::cmax(S.pmx, cm);
+          if (MINMAX) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) S.pmn = E::cmin(S.pmn, E::vmin(v[i]));
+          }
+          lazy_rescale<E, ENT>(S, cm, scale);
+#pragma unroll
+          for (int i = 0; i < 8; i++) accumulate_vec<E, ENT>(S, v[i], scale);
+        } else {
+          const int nr = (nv + 31) >> 5;
+#pragma unroll 1
+          for (int r = 0; r < nr; r++) {
+            const bool act = r * 32 + lane < nv;
+            uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
+            if (act) v = lds128(base + r * 512);
+            const typename E::MaxT cm = E::vmax(v);
+            S.pmx = E::cmax(S.pmx, cm);
+            if (MINMAX && act) S.pmn = E::cmin(S.pmn, E::vmin(v));
+            lazy_rescale<E, ENT>(S, cm, scale);
+            accumulate_vec<E, ENT>(S, v, scale);
+          }
+          ws.release(lane);
+        }
+      }
+      {
+        const float m = -S.negm;
+        const float s = S.s0 + S.s1, t = S.t0 + S.t1;
+        const float M = warp_max(m);
+        const float dl = m - M;
+        const float f = ex2_approx(dl);
+        const float Ssum = warp_sum(s * f);
+        const float Tt = warp_sum(f * fmaf(dl, s, t));
+        float mx = 0.f, mn = 0.f;
+        if (MINMAX) {
+          mx = warp_max(E::max_f(S.pmx));
+          mn = warp_min(E::min_f(S.pmn));
+        }
+        float* q = part + slot * 5 * WARPS;
+        int old = 0;
+        if (lane == 0) {
+          q[0 * WARPS + warp] = M;
+          q[1 * WARPS + warp] = Ssum;
+          q[2 * WARPS + warp] = Tt;
+          q[3 * WARPS + warp] = mx;
+          q[4 * WARPS + warp] = mn;
+          if (fetch) {
+            float* tk = tok + slot * 8;
+            tk[0] = xy;
+            tk[1] = t_prox;
+            tk[2] = t_old;
+            tk[3] = t_adv;
+            tk[4] = t_mask;
+            tk[5] = __int_as_float(t_lab);
+          }
+          __threadfence_block();
+          old = atomicAdd(&cnt[slot], 1);
+        }
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if (old == WARPS - 1) {
+          // ---- last warp to arrive: row statistics, the token's loss, the backward constants ----
+          __threadfence_block();
+          const volatile float* vq = q;
+          const bool has = lane < WARPS;
+          const float Mw = has ? vq[0 * WARPS + lane] : -kSentinel;
+          const float Sw = has ? vq[1 * WARPS + lane] : 0.f;
+          const float Tw = has ? vq[2 * WARPS + lane] : 0.f;
+          const float mxw = has ? vq[3 * WARPS + lane] : -INFINITY;
+          const float mnw = has ? vq[4 * WARPS + lane] : INFINITY;
+          const float Mr = warp_max(Mw);
+          const float dr = Mw - Mr;
+          const float fr = ex2_approx(dr);
+          const float Sr = warp_sum(Sw * fr);
+          const float Tr = warp_sum(fr * fmaf(dr, Sw, Tw));
+          float mxr = 0.f, mnr = 0.f;
+          if (MINMAX) {
+            mxr = warp_max(mxw);
+            mnr = warp_min(mnw);
+          }
+          if (lane == 0) {
+            cnt[slot] = 0;
+            const volatile float* tk = tok + slot * 8;
+            const float xyr = tk[0], px = tk[1], ol = tk[2], A = tk[3];
+            const bool m = tk[4] != 0.f;
+            const int lab = __float_as_int(tk[5]);
+            const float l2s = log2f(Sr);
+            const float lse_nat = (Mr + l2s) * kLn2;
+            const float lpv = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
+            p.lse[row] = lse_nat;
+            p.logp[row] = lpv;
+            if (p.ent) p.ent[row] = kLn2 * (l2s - Tr / Sr);
+            if (MINMAX) {
+              if (p.rowmax) p.rowmax[row] = mxr;
+              if (p.rowmin) p.rowmin[row] = mnr;
+            }
+            const PpoToken k = ppo_token(lpv, px, ol, A, m, p.clip_lo, p.clip_hi, p.c_clip, p.cap);
+            if (p.s_loss) p.s_loss[row] = k.pgw;
+            if (p.s_iw) p.s_iw[row] = k.ratio;
+            if (p.s_kl) p.s_kl[row] = k.kl;
+            if (p.s_clip) p.s_clip[row] = k.clip;
+            if (p.s_dual) p.s_dual[row] = k.dual;
+            if (p.s_bw) p.s_bw[row] = k.w;
+            if (p.s_bkl) p.s_bkl[row] = k.bkl;
+            if (p.s_bm) p.s_bm[row] = k.bmask;
+            if (m) {  // rows of a CTA are finalised strictly in order: a deterministic sum
+              cta_acc[0] += (double)k.pgw;
+              cta_acc[1] += 1.0;
+            }
+            // same operation order as ppo_loss_bwd_kernel + logprob_bwd_kernel (bit-identical dlogits)
+            const float glp = k.dlogp * up_over_n;
+            float* bc = bwdc + slot * 4;
+            bc[0] = -lse_nat * kLog2e;
+            bc[1] = -glp * p.inv_temp;
+            bc[2] = glp * p.inv_temp;
+            bc[3] = __int_as_float(lab);
+            __threadfence_block();
+            ready[slot] = use + 1;
+          }
+        }
+      }
+
+  };
+  // pass 2 of row-iteration `it` (backward, row from L2)
+  auto pass2 = [&](int it) {
     const int row = blockIdx.x + it * gridDim.x;
     const int slot = it & 1, use = it >> 1;
-    // one (rotating) warp fetches the token's scalars early
-    const bool fetch = (it % WARPS) == warp && lane == 0;
-    float xy = 0.f, t_prox = 0.f, t_old = 0.f, t_adv = 0.f, t_mask = 0.f;
-    int t_lab = -1;
-    if (fetch) {
-      const int64_t lab = p.labels[row];
-      const bool ok = lab >= 0 && lab < V;
-      xy = ok ? E::load1(p.logits, (int64_t)row * p.ld + lab) : __int_as_float(0x7fc00000);
-      t_lab = ok ? (int)lab : -1;
-      t_prox = p.prox[row];
-      t_old = p.old[row];
-      t_adv = p.adv[row];
-      t_mask = p.mask[row] ? 1.f : 0.f;
-    }
-
-    // ---------------- pass 1: forward statistics (row from HBM) ----------------
-    LaneState<E> S{kSentinel, 0.f, 0.f, 0.f, 0.f, E::max_init(), E::min_init()};
-    int left = ws.seg_len;
-    while (left > 0) {
-      const int nv = min(kChunkVec, left);
-      left -= nv;
-      const uint32_t base = ws.wait() + lane * 16;
-      if (nv == kChunkVec) {
-        uint4 v[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
-        ws.release(lane);
-        typename E::MaxT cm = E::vmax(v[0]);
-#pragma unroll
-        for (int i = 1; i < 8; i++) cm = E::cmax(cm, E::vmax(v[i]));
-        S.pmx = E::cmax(S.pmx, cm);
-        if (MINMAX) {
-#pragma unroll
-          for (int i = 0; i < 8; i++) S.pmn = E::cmin(S.pmn, E::vmin(v[i]));
-        }
-        lazy_rescale<E, ENT>(S, cm, scale);
-#pragma unroll
-        for (int i = 0; i < 8; i++) accumulate_vec<E, ENT>(S, v[i], scale);
-      } else {
-        const int nr = (nv + 31) >> 5;
-#pragma unroll 1
-        for (int r = 0; r < nr; r++) {
-          const bool act = r * 32 + lane < nv;
-          uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
-          if (act) v = lds128(base + r * 512);
-          const typename E::MaxT cm = E::vmax(v);
-          S.pmx = E::cmax(S.pmx, cm);
-          if (MINMAX && act) S.pmn = E::cmin(S.pmn, E::vmin(v));
-          lazy_rescale<E, ENT>(S, cm, scale);
-          accumulate_vec<E, ENT>(S, v, scale);
-        }
-        ws.release(lane);
-      }
-    }
-    {
-      const float m = -S.negm;
-      const float s = S.s0 + S.s1, t = S.t0 + S.t1;
-      const float M = warp_max(m);
-      const float dl = m - M;
-      const float f = ex2_approx(dl);
-      const float Ssum = warp_sum(s * f);
-      const float Tt = warp_sum(f * fmaf(dl, s, t));
-      float mx = 0.f, mn = 0.f;
-      if (MINMAX) {
-        mx = warp_max(E::max_f(S.pmx));
-        mn = warp_min(E::min_f(S.pmn));
-      }
-      float* q = part + slot * 5 * WARPS;
-      int old = 0;
+      // ---------------- pass 2: backward (row again, from L2) ----------------
       if (lane == 0) {
-        q[0 * WARPS + warp] = M;
-        q[1 * WARPS + warp] = Ssum;
-        q[2 * WARPS + warp] = Tt;
-        q[3 * WARPS + warp] = mx;
-        q[4 * WARPS + warp] = mn;
-        if (fetch) {
-          float* tk = tok + slot * 8;
-          tk[0] = xy;
-          tk[1] = t_prox;
-          tk[2] = t_old;
-          tk[3] = t_adv;
-          tk[4] = t_mask;
-          tk[5] = __int_as_float(t_lab);
-        }
-        __threadfence_block();
-        old = atomicAdd(&cnt[slot], 1);
-      }
-      old = __shfl_sync(0xffffffffu, old, 0);
-      if (old == WARPS - 1) {
-        // ---- last warp to arrive: row statistics, the token's loss, the backward constants ----
-        __threadfence_block();
-        const volatile float* vq = q;
-        const bool has = lane < WARPS;
-        const float Mw = has ? vq[0 * WARPS + lane] : -kSentinel;
-        const float Sw = has ? vq[1 * WARPS + lane] : 0.f;
-        const float Tw = has ? vq[2 * WARPS + lane] : 0.f;
-        const float mxw = has ? vq[3 * WARPS + lane] : -INFINITY;
-        const float mnw = has ? vq[4 * WARPS + lane] : INFINITY;
-        const float Mr = warp_max(Mw);
-        const float dr = Mw - Mr;
-        const float fr = ex2_approx(dr);
-        const float Sr = warp_sum(Sw * fr);
-        const float Tr = warp_sum(fr * fmaf(dr, Sw, Tw));
-        float mxr = 0.f, mnr = 0.f;
-        if (MINMAX) {
-          mxr = warp_max(mxw);
-          mnr = warp_min(mnw);
-        }
-        if (lane == 0) {
-          cnt[slot] = 0;
-          const volatile float* tk = tok + slot * 8;
-          const float xyr = tk[0], px = tk[1], ol = tk[2], A = tk[3];
-          const bool m = tk[4] != 0.f;
-          const int lab = __float_as_int(tk[5]);
-          const float l2s = log2f(Sr);
-          const float lse_nat = (Mr + l2s) * kLn2;
-          const float lpv = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
-          p.lse[row] = lse_nat;
-          p.logp[row] = lpv;
-          if (p.ent) p.ent[row] = kLn2 * (l2s - Tr / Sr);
-          if (MINMAX) {
-            if (p.rowmax) p.rowmax[row] = mxr;
-            if (p.rowmin) p.rowmin[row] = mnr;
-          }
-          const PpoToken k = ppo_token(lpv, px, ol, A, m, p.clip_lo, p.clip_hi, p.c_clip, p.cap);
-          if (p.s_loss) p.s_loss[row] = k.pgw;
-          if (p.s_iw) p.s_iw[row] = k.ratio;
-          if (p.s_kl) p.s_kl[row] = k.kl;
-          if (p.s_clip) p.s_clip[row] = k.clip;
-          if (p.s_dual) p.s_dual[row] = k.dual;
-          if (p.s_bw) p.s_bw[row] = k.w;
-          if (p.s_bkl) p.s_bkl[row] = k.bkl;
-          if (p.s_bm) p.s_bm[row] = k.bmask;
-          if (m) {  // rows of a CTA are finalised strictly in order: a deterministic sum
-            cta_acc[0] += (double)k.pgw;
-            cta_acc[1] += 1.0;
-          }
-          // same operation order as ppo_loss_bwd_kernel + logprob_bwd_kernel (bit-identical dlogits)
-          const float glp = k.dlogp * up_over_n;
-          float* bc = bwdc + slot * 4;
-          bc[0] = -lse_nat * kLog2e;
-          bc[1] = -glp * p.inv_temp;
-          bc[2] = glp * p.inv_temp;
-          bc[3] = __int_as_float(lab);
-          __threadfence_block();
-          ready[slot] = use + 1;
+        while (ready[slot] < use + 1) {
         }
       }
-    }
-
-    // ---------------- pass 2: backward (row again, from L2) ----------------
-    if (lane == 0) {
-      while (ready[slot] < use + 1) {
-      }
-    }
-    __syncwarp();
-    __threadfence_block();
-    const volatile float* bc = bwdc + slot * 4;
-    const float nlse2 = bc[0], A0 = bc[1], lab_add = bc[2];
-    const int lab = __float_as_int(bc[3]);
-    const int lvec = lab >= 0 ? lab / E::kPerVec : -1;
-    const int lsub = lab >= 0 ? lab % E::kPerVec : 0;
-    char* out_row = reinterpret_cast<char*>(p.dlogits) + ((int64_t)row * p.ld_out) * E::kBytes;
-    left = ws.seg_len;
-    int v0 = ws.sv + lane;
-    while (left > 0) {
-      const int nv = min(kChunkVec, left);
-      left -= nv;
-      const uint32_t base = ws.wait() + lane * 16;
-      if (nv == kChunkVec) {
-        uint4 v[8];
+      __syncwarp();
+      __threadfence_block();
+      const volatile float* bc = bwdc + slot * 4;
+      const float nlse2 = bc[0], A0 = bc[1], lab_add = bc[2];
+      const int lab = __float_as_int(bc[3]);
+      const int lvec = lab >= 0 ? lab / E::kPerVec : -1;
+      const int lsub = lab >= 0 ? lab % E::kPerVec : 0;
+      char* out_row = reinterpret_cast<char*>(p.dlogits) + ((int64_t)row * p.ld_out) * E::kBytes;
+      int left = ws.seg_len;
+      int v0 = ws.sv + lane;
+      while (left > 0) {
+        const int nv = min(kChunkVec, left);
+        left -= nv;
+        const uint32_t base = ws.wait() + lane * 16;
+        if (nv == kChunkVec) {
+          uint4 v[8];
 #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
-        ws.release(lane);
+          for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
+          ws.release(lane);
 #pragma unroll
-        for (int i = 0; i < 8; i++)
-          bwd_vec<E, false>(v[i], v0 + i * 32, true, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
-      } else {
-        const int nr = (nv + 31) >> 5;
+          for (int i = 0; i < 8; i++)
+            bwd_vec<E, false>(v[i], v0 + i * 32, true, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
+        } else {
+          const int nr = (nv + 31) >> 5;
 #pragma unroll 1
-        for (int r = 0; r < nr; r++) {
-          const bool act = r * 32 + lane < nv;
-          uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
-          if (act) v = lds128(base + r * 512);
-          bwd_vec<E, false>(v, v0 + r * 32, act, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
+          for (int r = 0; r < nr; r++) {
+            const bool act = r * 32 + lane < nv;
+            uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
+            if (act) v = lds128(base + r * 512);
+            bwd_vec<E, false>(v, v0 + r * 32, act, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
+          }
+          ws.release(lane);
         }
-        ws.release(lane);
+        v0 += kChunkVec;
       }
-      v0 += kChunkVec;
+  };
+  if (SKEW) {
+    // A0, A1, B0, A2, B1, ...: by the time a warp turns to the backward of row r it has streamed
+    // row r+1, so the last-arriving warp of row r has long published the backward constants
+    for (int it = 0; it < nrows; ++it) {
+      pass1(it);
+      if (it >= 1) pass2(it - 1);
+    }
+    if (nrows > 0) pass2(nrows - 1);
+  } else {
+    for (int it = 0; it < nrows; ++it) {
+      pass1(it);
+      pass2(it);
     }
   }
 
@@ -393,7 +420,7 @@ int set_smem_once(K kernel, int bytes) {
 
 template <int DT, bool MINMAX>
 int launch_fused(const FusedParams& p, cudaStream_t st) {
-  auto k = grpo_fused_kernel<DT, kFusedWarps, kFusedStages, MINMAX>;
+  auto k = grpo_fused_kernel<DT, kFusedWarps, kFusedStages, MINMAX, kFusedSkew>;
   constexpr int smem = FusedSmem<kFusedWarps, kFusedStages>::kBytes;
   int rc = set_smem_once(k, smem);
   if (rc) return rc;

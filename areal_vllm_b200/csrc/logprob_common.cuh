@@ -147,7 +147,10 @@ struct FwdSmem {
 // PASSES > 1 streams every row that many times back to back (the fused GRPO kernel reads a row for
 // the forward statistics and immediately again, out of L2, for the backward): all passes but the
 // last load with the normal L2 policy so the lines stay resident, the last with evict-first.
-template <int WARPS, int STAGES, int PASSES = 1>
+// SKEW (with PASSES == 2) orders the stream as A0, A1, B0, A2, B1, ... (A = first pass, B = second
+// pass of a row): the second pass of a row comes one row later, by which time whatever had to be
+// computed between the passes is long done.
+template <int WARPS, int STAGES, int PASSES = 1, bool SKEW = false>
 struct WarpStream {
   // static geometry
   int sv, seg_len;        // first vector / number of vectors of this warp's slice
@@ -155,6 +158,9 @@ struct WarpStream {
   // producer (lane 0 issues, every lane tracks the same state)
   const char* p_src;
   int p_left, p_rows_left, p_pass;
+  const char *a_ptr, *b_ptr;   // SKEW: slice start of the next first-pass / second-pass row
+  int a_left, a_done;          // SKEW: first-pass rows still to queue / already queued
+  int64_t row_stride;
   uint32_t p_dst, p_bar, ring_dst0, ring_bar0;
   int p_stage;
   uint64_t pol, pol_keep;
@@ -176,6 +182,10 @@ struct WarpStream {
     p_left = seg_len;
     p_pass = 0;
     p_rows_left = seg_len > 0 ? nrows : 0;
+    row_stride = (int64_t)gridDim.x * ld_bytes;
+    a_ptr = b_ptr = p_src;
+    a_left = nrows;
+    a_done = 0;
     ring_dst0 = smem_u32(my_data);
     ring_bar0 = smem_u32(my_bar);
     p_dst = c_dst = ring_dst0;
@@ -213,7 +223,19 @@ struct WarpStream {
       p_left -= nv;
       if (p_left == 0) {
         p_left = seg_len;
-        if (PASSES > 1 && ++p_pass < PASSES) {
+        if (SKEW) {
+          if (p_pass == 0) {  // finished a first pass
+            a_ptr += row_stride;
+            a_left--;
+            a_done++;
+            p_pass = (a_done >= 2 || a_left == 0) ? 1 : 0;
+          } else {            // finished a second pass: that row is complete
+            b_ptr += row_stride;
+            p_rows_left--;
+            p_pass = a_left > 0 ? 0 : 1;
+          }
+          p_src = p_pass == 0 ? a_ptr : b_ptr;
+        } else if (PASSES > 1 && ++p_pass < PASSES) {
           p_src -= (int64_t)seg_len * 16;  // same slice of the same row again
         } else {
           p_pass = 0;
