@@ -404,9 +404,14 @@ gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ val
 // piece take a branch-free path with constant multipliers. ~4x fewer instructions per token than the
 // per-token kernel, which was issue-bound (ncu: profiles/r01_ncu_gae.txt). Requires 16-byte aligned
 // rewards / adv / ret (else the per-token kernel is used).
-struct PieceSmem {
-  float a0[kTile];  // zero-carry advantages of the one piece that waits for a look-back carry
-  float v[kTile];   // its values
+constexpr int kVwPad = 64;  // value slots staged beyond the tile: one per sequence start in the tile
+struct __align__(16) PieceSmem {
+  float r[kTile];            // the tile's rewards, staged by one TMA bulk copy; once a block's rewards
+                             // are in registers the same slots take the zero-carry advantages of the
+                             // piece that waits for a look-back carry
+  float vw[kTile + kVwPad];  // the tile's window of `values`, staged by one TMA bulk copy
+  uint64_t bar;              // mbarrier of the two copies
+  uint64_t pad_;
 };
 
 struct PieceConst {
@@ -424,36 +429,68 @@ struct PiecePowers {
   float qtab[32];  // c^(4*(31-lane))
 };
 
-// One 128-token block of a piece. [ps, pe): the piece; tb: first token of the block (multiple of
-// 4); X: adv at token tb+128 (carry from the right); returns adv of the block's first token in X.
-template <bool STASH>
-__device__ __forceinline__ void piece_block(const PieceConst& K, const float* __restrict__ rewards,
-                                            const float* __restrict__ vseq, float* __restrict__ adv,
-                                            float* __restrict__ ret, int tb, int ps, int pe,
-                                            int last_tok, bool boot, int total, float& X,
-                                            PieceSmem& S, int tlo, int lane) {
-  const int t0 = tb + lane * 4;
-  const bool full = tb >= ps && tb + 128 <= pe;
+// The inputs of one 128-token block of a piece: 4 rewards and 5 values per lane (the 5th is the
+// next-value of the lane's last token), read from the tile's TMA-staged shared-memory copies.
+// The values of a piece are contiguous but shifted by the sequence index, so they are misaligned
+// against the 4-token lane groups by m = seq & 3 — the same for every lane: two aligned 16-byte
+// shared loads and a static select. Anything outside the staged windows (last partial tile, tiles
+// with more than kVwPad sequence starts) falls back to global loads.
+struct BlkData {
   float r[4], v[5];
-  if (full) {
-    const float4 r4 = *reinterpret_cast<const float4*>(rewards + t0);
-    r[0] = r4.x; r[1] = r4.y; r[2] = r4.z; r[3] = r4.w;
-#pragma unroll
-    for (int k = 0; k < 5; k++) v[k] = __ldg(vseq + t0 + k);
+};
+
+struct TileStage {
+  int tlo, rcount, vw0, vcount, total, vend;
+};
+
+__device__ __forceinline__ BlkData load_block(const PieceSmem& S, const TileStage& G,
+                                              const float* __restrict__ rewards,
+                                              const float* __restrict__ values, int seq, int tb,
+                                              int ps, int pe, int lane) {
+  BlkData D;
+  const int t0 = tb + lane * 4;
+  const int o = t0 - G.tlo;
+  if (tb - G.tlo + 128 <= G.rcount) {
+    const float4 r4 = *reinterpret_cast<const float4*>(&S.r[o]);
+    D.r[0] = r4.x; D.r[1] = r4.y; D.r[2] = r4.z; D.r[3] = r4.w;
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const int t = t0 + k;
-      r[k] = (t >= ps && t < pe) ? __ldg(rewards + t) : 0.f;
+    for (int k = 0; k < 4; k++)
+      D.r[k] = (o + k < G.rcount) ? S.r[o + k] : ((t0 + k < G.total) ? __ldg(rewards + t0 + k) : 0.f);
+  }
+  const int bi = t0 + seq - G.vw0;  // window index of the lane's first value
+  const int m = bi & 3;             // = (seq - vw0) & 3, warp-uniform
+  const int last = tb + 124 + seq - G.vw0 - m + 8;  // one past the last slot lane 31 touches
+  if (last <= G.vcount) {
+    const float4 w0 = *reinterpret_cast<const float4*>(&S.vw[bi - m]);
+    const float4 w1 = *reinterpret_cast<const float4*>(&S.vw[bi - m + 4]);
+    switch (m) {
+      case 0: D.v[0] = w0.x; D.v[1] = w0.y; D.v[2] = w0.z; D.v[3] = w0.w; D.v[4] = w1.x; break;
+      case 1: D.v[0] = w0.y; D.v[1] = w0.z; D.v[2] = w0.w; D.v[3] = w1.x; D.v[4] = w1.y; break;
+      case 2: D.v[0] = w0.z; D.v[1] = w0.w; D.v[2] = w1.x; D.v[3] = w1.y; D.v[4] = w1.z; break;
+      default: D.v[0] = w0.w; D.v[1] = w1.x; D.v[2] = w1.y; D.v[3] = w1.z; D.v[4] = w1.w; break;
     }
-    // values include slot pe: the next-value of the piece's last token (the sequence's bootstrap
-    // slot when the piece ends its sequence, the first value of the next tile otherwise)
+  } else {
 #pragma unroll
     for (int k = 0; k < 5; k++) {
       const int t = t0 + k;
-      v[k] = (t >= ps && t <= pe) ? __ldg(vseq + t) : 0.f;
+      D.v[k] = (t >= ps && t <= pe && t + seq < G.vend) ? __ldg(values + t + seq) : 0.f;
     }
   }
+  return D;
+}
+
+// One 128-token block of a piece. [ps, pe): the piece; tb: first token of the block (multiple of
+// 4); X: adv at token tb+128 (carry from the right); returns adv of the block's first token in X.
+template <bool STASH>
+__device__ __forceinline__ void piece_block(const PieceConst& K, const BlkData& D,
+                                            float* __restrict__ adv, float* __restrict__ ret, int tb,
+                                            int ps, int pe, int last_tok, bool boot, float& X,
+                                            PieceSmem& S, int tlo, int lane) {
+  const int t0 = tb + lane * 4;
+  const bool full = tb >= ps && tb + 128 <= pe;
+  const float* r = D.r;
+  const float* v = D.v;
   float d[4];
 #pragma unroll
   for (int k = 0; k < 4; k++) {
@@ -462,7 +499,18 @@ __device__ __forceinline__ void piece_block(const PieceConst& K, const float* __
     d[k] = fmaf(K.gamma, nv, r[k]) - v[k];
   }
   float A[4];
-  if (full) {
+  if (!full) {
+    // Ragged block: tokens outside the piece contribute delta = 0 and keep the multiplier c. That is
+    // exact: to the right of the piece's end the carry is 0 by construction (a piece that ends
+    // inside the tile starts from X = 0, and the piece that continues ends at the tile edge, which
+    // is a block edge), and what is computed left of the piece's start is never used.
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int t = t0 + k;
+      if (t < ps || t >= pe) d[k] = 0.f;
+    }
+  }
+  {
     // uniform multipliers: lane composite (c^4, L0), suffix scan over lanes with constants
     const float L3 = d[3];
     const float L2 = fmaf(K.c, L3, d[2]);
@@ -481,48 +529,20 @@ __device__ __forceinline__ void piece_block(const PieceConst& K, const float* __
     A[2] = fmaf(K.c2, carry, L2);
     A[1] = fmaf(K.c3, carry, L1);
     A[0] = fmaf(K.c4, carry, L0);
-  } else {
-    // ragged block: tokens outside the piece are the identity (a = 1, b = 0)
-    float a[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const int t = t0 + k;
-      const bool ok = t >= ps && t < pe;
-      a[k] = ok ? K.c : 1.f;
-      if (!ok) d[k] = 0.f;
-    }
-    const float L3 = d[3], P3 = a[3];
-    const float L2 = fmaf(a[2], L3, d[2]), P2 = a[2] * P3;
-    const float L1 = fmaf(a[1], L2, d[1]), P1 = a[1] * P2;
-    const float L0 = fmaf(a[0], L1, d[0]), P0 = a[0] * P1;
-    float Q = P0, Sx = L0;
-#pragma unroll
-    for (int sft = 1; sft < 32; sft <<= 1) {
-      const float q2 = __shfl_down_sync(0xffffffffu, Q, sft);
-      const float s2 = __shfl_down_sync(0xffffffffu, Sx, sft);
-      if (lane + sft < 32) {
-        Sx = fmaf(Q, s2, Sx);
-        Q = Q * q2;
-      }
-    }
-    float Qr = __shfl_down_sync(0xffffffffu, Q, 1);
-    float Sr = __shfl_down_sync(0xffffffffu, Sx, 1);
-    if (lane == 31) {
-      Qr = 1.f;
-      Sr = 0.f;
-    }
-    const float carry = fmaf(Qr, X, Sr);
-    A[3] = fmaf(P3, carry, L3);
-    A[2] = fmaf(P2, carry, L2);
-    A[1] = fmaf(P1, carry, L1);
-    A[0] = fmaf(P0, carry, L0);
   }
-  X = __shfl_sync(0xffffffffu, A[0], 0);
+  if (tb >= ps) {
+    X = __shfl_sync(0xffffffffu, A[0], 0);
+  } else {
+    // the piece starts inside this block: hand back adv at its first token
+    const int rel = ps - tb;
+    const float sel = (rel & 3) == 0 ? A[0] : ((rel & 3) == 1 ? A[1] : ((rel & 3) == 2 ? A[2] : A[3]));
+    X = __shfl_sync(0xffffffffu, sel, rel >> 2);
+  }
   if (STASH) {
-    // the piece's carry is not known yet: keep zero-carry adv and v for the final sweep
+    // the piece's carry is not known yet: keep the zero-carry adv for the final sweep (its values
+    // stay in the staged window)
     const int o = t0 - tlo;
-    *reinterpret_cast<float4*>(&S.a0[o]) = make_float4(A[0], A[1], A[2], A[3]);
-    *reinterpret_cast<float4*>(&S.v[o]) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(&S.r[o]) = make_float4(A[0], A[1], A[2], A[3]);
   } else if (full) {
     *reinterpret_cast<float4*>(adv + t0) = make_float4(A[0], A[1], A[2], A[3]);
     *reinterpret_cast<float4*>(ret + t0) = make_float4(A[0] + v[0], A[1] + v[1], A[2] + v[2], A[3] + v[3]);
@@ -536,7 +556,24 @@ __device__ __forceinline__ void piece_block(const PieceConst& K, const float* __
       }
     }
   }
-  (void)total;
+}
+
+// Pre-pass of the piece-wise kernel: for every tile, the sequence that owns its first token and that
+// sequence's bounds and bootstrap flag. One thread per tile; all the dependent binary-search loads of
+// all tiles overlap here instead of sitting at the head of every tile's critical path.
+__global__ void __launch_bounds__(256)
+gae_tile_index_kernel(const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot, int batch,
+                      int num_tiles, int4* __restrict__ table) {
+  const int g = blockIdx.x * 256 + threadIdx.x;
+  if (g >= num_tiles) return;
+  const int x = g * kTile;
+  int lo = 1, hi = batch + 1;  // #{k in [1,batch] : cu[k] <= x}
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cu[mid] <= x) lo = mid + 1; else hi = mid;
+  }
+  const int i = lo - 1;
+  table[g] = make_int4(i, cu[i], cu[i + 1], (int)boot[i]);
 }
 
 __global__ void __launch_bounds__(kScanWarps * 32, 6)
@@ -544,7 +581,8 @@ gae_pieces_kernel(const float* __restrict__ rewards, const float* __restrict__ v
                   const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot,
                   float* __restrict__ adv, float* __restrict__ ret, int batch, int total,
                   float gamma, const PiecePowers PW, uint64_t* __restrict__ state,
-                  unsigned int* __restrict__ ticket_ctr, int num_tiles) {
+                  unsigned int* __restrict__ ticket_ctr, const int4* __restrict__ table,
+                  int num_tiles) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PieceSmem& S = reinterpret_cast<PieceSmem*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -558,61 +596,120 @@ gae_pieces_kernel(const float* __restrict__ rewards, const float* __restrict__ v
 #pragma unroll
   for (int j = 0; j < 5; j++) K.cpow[j] = PW.cpow[j];
   K.qlane = PW.qtab[lane];
+  if (lane == 0) {
+    mbar_init(&S.bar, 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  uint32_t bar_phase = 0;
+  const uint64_t pol = policy_evict_first();
 
-  while (true) {
-    unsigned int ticket = 0;
-    if (lane == 0) ticket = atomicAdd(ticket_ctr, 1u);
-    ticket = __shfl_sync(0xffffffffu, ticket, 0);
-    if (ticket >= (unsigned)num_tiles) break;
+  // The ticket and the index-table entry of the NEXT tile are fetched while the current one is
+  // being processed (every warp does the same, so neighbouring tiles still start at about the same
+  // time and the look-back finds its right neighbour in progress).
+  // {sequence owning the tile's first token, its start, its end, its bootstrap flag}: from the
+  // pre-pass table for large inputs, searched here for small ones (where one more launch would
+  // cost more than the search)
+  auto tile_entry = [&](unsigned int tk) {
+    const int gg = num_tiles - 1 - (int)tk;
+    if (table) return table[gg];
+    const int i = count_ends_le(cu, batch, gg * kTile, lane);
+    return make_int4(i, cu[i], cu[i + 1], (int)boot[i]);
+  };
+  unsigned int ticket = 0;
+  if (lane == 0) ticket = atomicAdd(ticket_ctr, 1u);
+  ticket = __shfl_sync(0xffffffffu, ticket, 0);
+  int4 te = make_int4(0, 0, 0, 0);
+  if (ticket < (unsigned)num_tiles) te = tile_entry(ticket);
+  while (ticket < (unsigned)num_tiles) {
     const int g = num_tiles - 1 - (int)ticket;
     const int tlo = g * kTile;
     const int thi = min(tlo + kTile, total);
-    const int i_lo = count_ends_le(cu, batch, tlo, lane);  // sequence that owns token tlo
+    unsigned int nticket = 0;
+    if (lane == 0) nticket = atomicAdd(ticket_ctr, 1u);
+    const int i_lo = te.x;
+    // stage the tile: its rewards and its window of values, one TMA bulk copy each
+    TileStage G;
+    G.tlo = tlo;
+    G.total = total;
+    G.vend = total + batch;
+    G.rcount = (thi - tlo) & ~3;
+    G.vw0 = (tlo + i_lo) & ~3;
+    G.vcount = min(kTile + kVwPad, (G.vend - G.vw0) & ~3);
+    __syncwarp();  // every lane is done reading the previous tile's staged data
+    if (lane == 0 && G.rcount + G.vcount > 0) {
+      mbar_expect_tx(&S.bar, (uint32_t)(G.rcount + G.vcount) * 4u);
+      if (G.rcount > 0) bulk_g2s(S.r, rewards + tlo, (uint32_t)G.rcount * 4u, &S.bar, pol);
+      if (G.vcount > 0) bulk_g2s(S.vw, values + G.vw0, (uint32_t)G.vcount * 4u, &S.bar, pol);
+    }
 
     bool first = true;          // the piece that contains tlo has not been published yet
     int carry_ps = -1;          // first token of the piece that waits for the look-back carry
+    int carry_seq = 0;          // its sequence
     float carry_first = 0.f;    // its zero-carry adv at carry_ps
     bool carry_is_first = false;
-    bool done = false;
-    for (int base = i_lo; !done; base += 32) {
-      const int idx = base + lane;
-      const int cs = idx <= batch ? cu[idx] : 0x7fffffff;
-      const int ce = idx < batch ? cu[idx + 1] : 0x7fffffff;
-      const int bt = idx < batch ? (int)boot[idx] : 0;
+
+    auto do_piece = [&](int seq, int s, int e, bool b) {
+      const int ps = max(s, tlo), pe = min(e, thi);
+      const bool ends_here = e <= thi;
+      const bool waits = !ends_here;  // continues into the tile on the right: needs its adv
+      const int last_tok = ends_here ? e - 1 : -1;  // value of token t of sequence seq: values[t + seq]
+      float X = 0.f;
+      const int b_hi = (pe - 1 - tlo) >> 7, b_lo = (ps - tlo) >> 7;
+#pragma unroll 1
+      for (int blk = b_hi; blk >= b_lo; blk--) {
+        const BlkData cur = load_block(S, G, rewards, values, seq, tlo + blk * 128, ps, pe, lane);
+        if (waits) piece_block<true>(K, cur, adv, ret, tlo + blk * 128, ps, pe, last_tok, b, X, S, tlo, lane);
+        else piece_block<false>(K, cur, adv, ret, tlo + blk * 128, ps, pe, last_tok, b, X, S, tlo, lane);
+      }
+      if (waits) {
+        carry_ps = ps;
+        carry_seq = seq;
+        carry_first = X;
+        carry_is_first = first;
+      }
+      if (first) {
+        first = false;
+        if (lane == 0 && g > 0) st_state(&state[g], waits ? kFlagAgg : kFlagIncl, X);
+      }
+    };
+
+    // the sequences after the first one: their bounds are fetched while the first piece is scanned
+    int base = i_lo + 1;
+    int idx = base + lane;
+    int cs = idx <= batch ? cu[idx] : 0x7fffffff;
+    int ce = idx < batch ? cu[idx + 1] : 0x7fffffff;
+    int bt = idx < batch ? (int)boot[idx] : 0;
+    if (G.rcount + G.vcount > 0) {
+      while (!mbar_try_wait(&S.bar, bar_phase)) {
+      }
+      bar_phase ^= 1;
+    }
+    nticket = __shfl_sync(0xffffffffu, nticket, 0);
+    int4 nte = make_int4(0, 0, 0, 0);
+    if (nticket < (unsigned)num_tiles) nte = tile_entry(nticket);
+    do_piece(i_lo, te.y, te.z, te.w != 0);
+    bool done = te.z >= thi;
+    while (!done) {
 #pragma unroll 1
       for (int k = 0; k < 32; k++) {
         const int seq = base + k;
-        const int s = __shfl_sync(0xffffffffu, cs, k);
-        const int e = __shfl_sync(0xffffffffu, ce, k);
-        const bool b = __shfl_sync(0xffffffffu, bt, k) != 0;
-        if (seq >= batch || s >= thi) {
+        const int s_ = __shfl_sync(0xffffffffu, cs, k);
+        const int e_ = __shfl_sync(0xffffffffu, ce, k);
+        const bool b_ = __shfl_sync(0xffffffffu, bt, k) != 0;
+        if (seq >= batch || s_ >= thi) {
           done = true;
           break;
         }
-        if (e <= s) continue;  // empty sequence
-        const int ps = max(s, tlo), pe = min(e, thi);
-        const bool ends_here = e <= thi;
-        const bool waits = !ends_here;  // continues into the tile on the right: needs its adv
-        const float* vseq = values + seq;  // value of token t of this sequence sits at t + seq
-        const int last_tok = ends_here ? e - 1 : -1;
-        float X = 0.f;
-        const int b_hi = (pe - 1 - tlo) >> 7, b_lo = (ps - tlo) >> 7;
-        if (waits) {
-#pragma unroll 1
-          for (int blk = b_hi; blk >= b_lo; blk--)
-            piece_block<true>(K, rewards, vseq, adv, ret, tlo + blk * 128, ps, pe, last_tok, b, total, X, S, tlo, lane);
-          carry_ps = ps;
-          carry_first = X;
-          carry_is_first = first;
-        } else {
-#pragma unroll 1
-          for (int blk = b_hi; blk >= b_lo; blk--)
-            piece_block<false>(K, rewards, vseq, adv, ret, tlo + blk * 128, ps, pe, last_tok, b, total, X, S, tlo, lane);
-        }
-        if (first) {
-          first = false;
-          if (lane == 0 && g > 0) st_state(&state[g], waits ? kFlagAgg : kFlagIncl, X);
-        }
+        if (e_ <= s_) continue;  // empty sequence
+        do_piece(seq, s_, e_, b_);
+      }
+      if (!done) {
+        base += 32;
+        idx = base + lane;
+        cs = idx <= batch ? cu[idx] : 0x7fffffff;
+        ce = idx < batch ? cu[idx + 1] : 0x7fffffff;
+        bt = idx < batch ? (int)boot[idx] : 0;
       }
     }
 
@@ -641,8 +738,9 @@ gae_pieces_kernel(const float* __restrict__ rewards, const float* __restrict__ v
       for (int blk = b_hi; blk >= b_lo; blk--) {
         const int o = blk * 128 + lane * 4;
         const int t0 = tlo + o;
-        const float4 a4 = *reinterpret_cast<const float4*>(&S.a0[o]);
-        const float4 v4 = *reinterpret_cast<const float4*>(&S.v[o]);
+        const float4 a4 = *reinterpret_cast<const float4*>(&S.r[o]);
+        const BlkData D = load_block(S, G, rewards, values, carry_seq, tlo + blk * 128, carry_ps, thi, lane);
+        const float4 v4 = make_float4(D.v[0], D.v[1], D.v[2], D.v[3]);
         // multiplier of the carry for token t: c^(thi - t)
         const float m3 = ex2_approx(K.lc * (float)(thi - (t0 + 3)));
         const float m2 = m3 * K.c, m1 = m2 * K.c, m0 = m1 * K.c;
@@ -666,6 +764,8 @@ gae_pieces_kernel(const float* __restrict__ rewards, const float* __restrict__ v
       }
       __syncwarp();
     }
+    ticket = nticket;
+    te = nte;
   }
 }
 
@@ -693,7 +793,8 @@ extern "C" {
 size_t b200rl_gae_workspace_bytes(int32_t batch, int64_t total) {
   (void)batch;
   if (total < 0) return 0;
-  return b200rl::scan_ws(nullptr, total).bytes;
+  const b200rl::ScanWs W = b200rl::scan_ws(nullptr, total);
+  return W.bytes + (size_t)W.num_tiles * sizeof(int4);  // look-back state + the tile index table
 }
 
 int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
@@ -724,21 +825,22 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
     B200RL_REQUIRE(workspace != nullptr, "SCAN mode needs a workspace");
     B200RL_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "workspace must be 256-B aligned");
     ScanWs W = scan_ws(workspace, total);
-    if (workspace_bytes < W.bytes) {
-      set_last_error("gae workspace too small: %zu < %zu", workspace_bytes, W.bytes);
+    if (workspace_bytes < W.bytes + (size_t)W.num_tiles * sizeof(int4)) {
+      set_last_error("gae workspace too small: %zu < %zu", workspace_bytes,
+                     W.bytes + (size_t)W.num_tiles * sizeof(int4));
       return B200RL_EWORKSPACE;
     }
     B200RL_CUDA(cudaMemsetAsync(workspace, 0, W.bytes, st));
     static bool attr_set[64] = {false};
     const size_t smem = sizeof(ScanSmem) * kScanWarps;
-    static_assert(sizeof(PieceSmem) == sizeof(ScanSmem), "both scan kernels use 8 KiB per warp");
+    const size_t smem_p = sizeof(PieceSmem) * kScanWarps;
     int dev = 0;
     B200RL_CUDA(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
       B200RL_CUDA(cudaFuncSetAttribute(gae_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
       B200RL_CUDA(cudaFuncSetAttribute(gae_pieces_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem));
+                                       (int)smem_p));
       attr_set[dev] = true;
     }
     int grid = (W.num_tiles + kScanWarps - 1) / kScanWarps;
@@ -748,7 +850,7 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
     // sequence piece, so batches of very short sequences (< 128 tokens on average) stay on the
     // per-token kernel (measured: 500k sequences of 1-64 tokens, 103 us vs 232 us).
     const bool vec_ok = ((reinterpret_cast<uintptr_t>(rewards) | reinterpret_cast<uintptr_t>(adv) |
-                          reinterpret_cast<uintptr_t>(ret)) & 15) == 0;
+                          reinterpret_cast<uintptr_t>(ret) | reinterpret_cast<uintptr_t>(values)) & 15) == 0;
     if (vec_ok && total >= (int64_t)batch * 128) {
       PiecePowers PW;
       const double c = (double)gamma * (double)lam;  // the kernels use fl32(gamma*lam) as c
@@ -761,9 +863,17 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
       PW.cT = (float)pow(cf, (double)kTile);
       for (int j = 0; j < 5; j++) PW.cpow[j] = (float)pow(cf, 4.0 * (double)(1 << j));
       for (int l = 0; l < 32; l++) PW.qtab[l] = (float)pow(cf, 4.0 * (double)(31 - l));
-      gae_pieces_kernel<<<grid, kScanWarps * 32, smem, st>>>(rewards, values, cu_seqlens, bootstrap,
+      int4* table = nullptr;
+      if (W.num_tiles >= 4096) {  // below that the in-kernel search is cheaper than another launch
+        table = reinterpret_cast<int4*>((char*)workspace + W.bytes);
+        gae_tile_index_kernel<<<(W.num_tiles + 255) / 256, 256, 0, st>>>(cu_seqlens, bootstrap, batch,
+                                                                        W.num_tiles, table);
+      }
+      int grid_p = (W.num_tiles + kScanWarps - 1) / kScanWarps;
+      if (grid_p > sm_count() * 6) grid_p = sm_count() * 6;  // 6 CTAs x 4 warps x 8.3 KiB per SM
+      gae_pieces_kernel<<<grid_p, kScanWarps * 32, smem_p, st>>>(rewards, values, cu_seqlens, bootstrap,
                                                           adv, ret, batch, (int)total, gamma, PW,
-                                                          W.state, W.ticket, W.num_tiles);
+                                                          W.state, W.ticket, table, W.num_tiles);
       return check_launch("gae_pieces_kernel");
     }
     gae_scan_kernel<<<grid, kScanWarps * 32, smem, st>>>(rewards, values, cu_seqlens, bootstrap,
