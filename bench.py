@@ -249,7 +249,46 @@ def run_extras(dev, peak):
             ts.append(e0.elapsed_time(e1))
         return float(np.median(ts))
 
-    out = {"gae": [], "interval_op": []}
+    out = {"gae": [], "interval_op": [], "torch_gpu_path": None}
+    # The reference's own GPU path for H1+H2 — the same torch ops (areal/utils/functional.py:10-26,
+    # 124-188), eager, in 1024-row chunks like its wrappers — timed on this B200: the kernels to beat.
+    try:
+        import torch.nn.functional as F
+
+        Tt = 4096
+        gen = torch.Generator(device=dev).manual_seed(11)
+        lg = (torch.randn(Tt, V, generator=gen, device=dev) * 2).bfloat16()
+        ids = torch.randint(0, V, (Tt,), generator=gen, device=dev)
+        lp0 = -torch.rand(Tt, generator=gen, device=dev) * 4
+        old, prox = lp0 + 0.05, lp0 + 0.02
+        advt = torch.randn(Tt, generator=gen, device=dev)
+        msk = torch.rand(Tt, generator=gen, device=dev) < 0.7
+
+        def torch_step():
+            x = lg.detach().requires_grad_(True)
+            lps, ents = [], []
+            for lo in range(0, Tt, 1024):
+                la = F.log_softmax(x[lo:lo + 1024].float() / TEMPERATURE, dim=-1)
+                ents.append(-(la.exp() * la).sum(-1))
+                lps.append(la.gather(-1, ids[lo:lo + 1024, None]).squeeze(-1))
+            lp = torch.cat(lps)
+            n = msk.count_nonzero() or 1
+            ratio = torch.where(msk, torch.exp(lp - prox), 0)
+            pg = torch.max(-advt * ratio, -advt * ratio.clamp(1 - EPS_CLIP, 1 + EPS_CLIP))
+            bw = (prox - old).exp()
+            bm = (bw <= CAP) & msk
+            loss = torch.where(msk, pg * torch.where(bm, bw, 0.0), 0).sum() / n
+            _ = x.detach().min(-1).values, x.detach().max(-1).values
+            loss.backward()
+
+        ms = timeit(torch_step, iters=5, warm=2)
+        out["torch_gpu_path"] = {"what": "eager torch restatement of the reference GPU path (log_softmax/gather/"
+                                         "entropy in 1024-row chunks, PPO loss, min/max, backward) on this GPU",
+                                 "tokens": Tt, "ms": ms, "tokens_per_s": Tt / (ms * 1e-3)}
+        del lg
+        torch.cuda.empty_cache()
+    except Exception as e:  # an OOM or similar here must not cost the headline line
+        out["torch_gpu_path"] = {"error": repr(e)[:200]}
     for name, B, lo, hi, seed in (("cfg1: 256 seqs, len 64-2048", 256, 64, 2048, 1),
                                   ("cfg1 length law x256: 65536 seqs", 65536, 64, 2048, 2)):
         rng = np.random.default_rng(seed)
@@ -561,6 +600,35 @@ def main_b200rl(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu_baseline = run_cpu_baseline()
     extras = None
+    if world > 1 and not args.no_extras:
+        # GAE shards by sequence too: every rank scans its own 65,536 sequences (weak scaling)
+        import areal_vllm_b200 as pkg
+        rng = np.random.default_rng(2 + rank)
+        lens = rng.integers(64, 2049, 65536)
+        tot = int(lens.sum())
+        r_ = torch.randn(tot, device=dev)
+        v_ = torch.randn(tot + 65536, device=dev)
+        cu_ = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)).to(dev)
+        b_ = torch.ones(65536, dtype=torch.bool, device=dev)
+        res = {}
+        for gamma, lam in ((0.99, 0.95), (1.0, 1.0)):
+            for _ in range(3):
+                pkg.ppo_functional.cugae1d_nolp_misalign_func(r_, v_, cu_, b_, gamma, lam)
+            torch.cuda.synchronize()
+            dist.barrier()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record()
+            for _ in range(10):
+                pkg.ppo_functional.cugae1d_nolp_misalign_func(r_, v_, cu_, b_, gamma, lam)
+            g1.record()
+            torch.cuda.synchronize()
+            tm = torch.tensor([g0.elapsed_time(g1) / 10, float(tot)], device=dev, dtype=torch.float64)
+            tmax = tm.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tm, op=dist.ReduceOp.SUM)
+            res[f"gamma={gamma},lam={lam}"] = {"tokens_all_ranks": float(tm[1]), "ms_max_over_ranks": float(tmax[0]),
+                                               "tokens_per_s": float(tm[1]) / (float(tmax[0]) * 1e-3)}
+        extras = {"gae_weak_scaling_65536_seqs_per_rank": res}
     if rank == 0 and world == 1 and not args.no_extras:
         del logits_bufs[:]
         torch.cuda.empty_cache()
