@@ -302,7 +302,7 @@ def run_extras(dev, peak):
         for gamma, lam in ((0.99, 0.95), (1.0, 1.0)):
             ms = timeit(lambda: pkg.ppo_functional.cugae1d_nolp_misalign_func(r, v, cu, b, gamma, lam))
             rec = {"workload": name, "gamma": gamma, "lam": lam, "tokens": total,
-                   "kernel": "gae_scan_kernel" if gamma * lam <= 0.99 else "gae_serial_kernel",
+                   "kernel": "gae_pieces_kernel (tiled scan)" if gamma * lam <= 0.99 else "gae_serial_kernel",
                    "us": ms * 1e3, "tokens_per_s": total / (ms * 1e-3),
                    "hbm_frac_of_measured_peak": 16.0 * total / (ms * 1e-3) / 1e9 / peak}
             if B == 256:  # CPU baseline: C port of pygae1d_nolp_misalign, one thread (the python
@@ -483,12 +483,12 @@ def main_b200rl(args):
             traffic = per_row * (sum(T for _, _, T in bwd_events) / max(len(bwd_events), 1))
     achieved = bwd_bytes / (bwd_ms * 1e-3) / 1e9
     roofline = {
-        "kernel": "logprob_bwd_bf16_kernel (+ppo_loss_bwd_kernel, <0.1%)", "bound": "hbm",
+        "kernel": "logprob_bwd_kernel<bf16> (+ppo_loss_bwd_kernel, <0.1%)", "bound": "hbm",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         "traffic": traffic, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": bwd_bytes / max(len(bwd_events), 1),
         "algorithmic_bytes_per_token": 4 * V, "launches_timed": len(bwd_events),
-        "fwd": {"kernel": "logprob_fwd_bf16_kernel<ENT,MINMAX> (+ppo_loss_fwd, stats)",
+        "fwd": {"kernel": "logprob_fwd_kernel<bf16,ENT,MINMAX> (+ppo_loss_fwd_kernel, roll/bool casts)",
                 "achieved": fwd_bytes / (fwd_ms * 1e-3) / 1e9,
                 "frac": fwd_bytes / (fwd_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_token": 2 * V},
         "fwd_bwd_frac_of_peak": (fwd_bytes + bwd_bytes) / ((fwd_ms + bwd_ms) * 1e-3) / 1e9 / peak,
