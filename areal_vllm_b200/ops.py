@@ -476,6 +476,128 @@ def ppo_loss_bwd(dlogp, grad_loss, denom):
 
 
 # --------------------------------------------------------------------------------------------
+# critic (value) loss and packed rewards: companions of the GAE path (legacy PPO interface)
+# --------------------------------------------------------------------------------------------
+def _raw_critic_loss_fwd(value: Tensor, old_value: Tensor, target_value: Tensor,
+                         mask: Optional[Tensor], eps: float, loss_type: int, delta: float) -> List[Tensor]:
+    """-> [loss(0-d), denom(1), dvalue, stat_loss, clip_mask(u8)]"""
+    _lib.require_cuda(value=value, old_value=old_value, target_value=target_value)
+    shape, dev = value.shape, value.device
+
+    def flat(t: Tensor, name: str) -> Tensor:
+        if t.shape != shape:
+            raise RuntimeError(f"{name} has shape {tuple(t.shape)}, expected {tuple(shape)}")
+        if t.dtype != torch.float32:
+            raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+        return t.detach().contiguous().view(-1)
+
+    v, ov, tv = flat(value, "value"), flat(old_value, "old_value"), flat(target_value, "target_value")
+    mk = None
+    if mask is not None:
+        if mask.shape != shape:
+            raise RuntimeError(f"loss_mask has shape {tuple(mask.shape)}, expected {tuple(shape)}")
+        _lib.require_cuda(loss_mask=mask)
+        mk = (mask if mask.dtype == torch.bool else mask != 0).contiguous().view(-1).view(torch.uint8)
+    T = v.numel()
+    loss = torch.empty((), dtype=torch.float32, device=dev)
+    denom = torch.empty(1, dtype=torch.float32, device=dev)
+    dvalue, s_loss = torch.empty_like(v), torch.empty_like(v)
+    s_clip = torch.empty(T, dtype=torch.uint8, device=dev)
+    ws = _lib.workspace(lib.b200rl_critic_loss_workspace_bytes(T), dev)
+    with _on(dev):
+        rc = lib.b200rl_critic_loss_fwd(ptr(v), ptr(ov), ptr(tv), ptr(mk), T, float(eps), int(loss_type),
+                                        float(delta), ptr(s_loss), ptr(s_clip), ptr(dvalue), ptr(loss),
+                                        ptr(denom), ptr(ws), ws.numel(), stream_handle(dev))
+    check(rc, "b200rl_critic_loss_fwd")
+    return [loss, denom, dvalue.view(shape), s_loss.view(shape), s_clip.view(shape)]
+
+
+critic_loss_fwd_op = torch.library.custom_op("b200rl::critic_loss_fwd", _raw_critic_loss_fwd, mutates_args=())
+
+
+@critic_loss_fwd_op.register_fake
+def _(value, old_value, target_value, mask, eps, loss_type, delta):
+    return [value.new_empty((), dtype=torch.float32), value.new_empty((1,), dtype=torch.float32),
+            torch.empty_like(value), torch.empty_like(value), torch.empty_like(value, dtype=torch.uint8)]
+
+
+def _critic_backward(ctx, grads):
+    dvalue, denom = ctx.saved_tensors
+    g = None if grads[0] is None else ppo_loss_bwd_op(dvalue, grads[0], denom)
+    return (g,) + (None,) * 6
+
+
+critic_loss_fwd_op.register_autograd(
+    _critic_backward, setup_context=lambda ctx, inputs, output: ctx.save_for_backward(output[2], output[1]))
+
+
+class _CriticLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, value, old_value, target_value, mask, eps, loss_type, delta):
+        out = _raw_critic_loss_fwd(value, old_value, target_value, mask, eps, loss_type, delta)
+        ctx.save_for_backward(out[2], out[1])
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(*out[1:])
+        return tuple(out)
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        dvalue, denom = ctx.saved_tensors
+        g = None if g_loss is None else _raw_ppo_loss_bwd(dvalue, g_loss, denom)
+        return (g,) + (None,) * 6
+
+
+def critic_loss_fwd(value, old_value, target_value, mask, eps, loss_type, delta):
+    args = (value, old_value, target_value, mask, eps, loss_type, delta)
+    if not _eager():
+        return critic_loss_fwd_op(*args)
+    if value.requires_grad and torch.is_grad_enabled():
+        return list(_CriticLossFn.apply(*args))
+    return _raw_critic_loss_fwd(*args)
+
+
+def _raw_packed_rewards(log_probs: Tensor, ref_log_probs: Tensor, reward_score: Tensor,
+                        short1cu_seqlens: Tensor, seq_no_eos_mask: Tensor, kl_ctl: float,
+                        clip_reward_value: float, mask_no_eos_with_zero: bool) -> List[Tensor]:
+    """-> [kl_rewards, tot_rewards]"""
+    _lib.require_cuda(log_probs=log_probs, ref_log_probs=ref_log_probs, reward_score=reward_score,
+                      short1cu_seqlens=short1cu_seqlens, seq_no_eos_mask=seq_no_eos_mask)
+    dev = log_probs.device
+    if log_probs.dim() != 1 or ref_log_probs.shape != log_probs.shape:
+        raise RuntimeError("log_probs and ref_log_probs must be 1-D and of the same length")
+    lp = log_probs.detach().to(torch.float32).contiguous()
+    rf = ref_log_probs.detach().to(torch.float32).contiguous()
+    sc = reward_score.detach().to(torch.float32).contiguous().view(-1)
+    cu = short1cu_seqlens.to(torch.int32).contiguous().view(-1)
+    ne = (seq_no_eos_mask if seq_no_eos_mask.dtype == torch.bool else seq_no_eos_mask != 0)
+    ne = ne.contiguous().view(-1).view(torch.uint8)
+    B = cu.numel() - 1
+    if sc.numel() != B or ne.numel() != B:
+        raise RuntimeError(f"reward_score/seq_no_eos_mask need {B} entries (one per sequence)")
+    kl, tot = torch.empty_like(lp), torch.empty_like(lp)
+    with _on(dev):
+        rc = lib.b200rl_packed_rewards(ptr(lp), ptr(rf), ptr(sc), ptr(cu), ptr(ne), B, lp.numel(),
+                                       float(kl_ctl), float(clip_reward_value),
+                                       int(bool(mask_no_eos_with_zero)), ptr(kl), ptr(tot),
+                                       stream_handle(dev))
+    check(rc, "b200rl_packed_rewards")
+    return [kl, tot]
+
+
+packed_rewards_op = torch.library.custom_op("b200rl::packed_rewards", _raw_packed_rewards, mutates_args=())
+
+
+@packed_rewards_op.register_fake
+def _(log_probs, ref_log_probs, reward_score, short1cu_seqlens, seq_no_eos_mask, kl_ctl,
+      clip_reward_value, mask_no_eos_with_zero):
+    return [torch.empty_like(log_probs, dtype=torch.float32), torch.empty_like(log_probs, dtype=torch.float32)]
+
+
+def packed_rewards(*args):
+    return _raw_packed_rewards(*args) if _eager() else packed_rewards_op(*args)
+
+
+# --------------------------------------------------------------------------------------------
 # H2 masked moments / normalisation
 # --------------------------------------------------------------------------------------------
 def _raw_masked_moments(

@@ -148,3 +148,47 @@ def actor_loss_fn(
         stat["behave_approx_kl"] = det[10]
         stat["behave_mask"] = det[11].view(torch.bool)
     return out[0], stat
+
+
+def critic_loss_fn(
+    value: torch.Tensor,
+    old_value: torch.Tensor,
+    target_value: torch.Tensor,
+    value_eps_clip: float,
+    loss_mask: Optional[torch.Tensor] = None,
+    loss_fn_type: str = "mse",
+) -> Tuple[torch.Tensor, Dict]:
+    """Clipped value loss (ref ppo_functional.py:171-225; huber delta 10.0 as at :197). One launch
+    yields the scalar, both stats and d loss / d value. Like the reference the masked mean divides
+    by ``count_nonzero(mask)`` with no guard, so an all-false mask gives nan."""
+    assert value.dtype == torch.float32
+    assert old_value.dtype == torch.float32
+    assert target_value.dtype == torch.float32
+    if loss_fn_type == "huber":
+        kind = 1
+    elif loss_fn_type == "mse":
+        kind = 0
+    else:
+        raise NotImplementedError(f"Unknown loss fn type: {loss_fn_type}")
+    out = ops.critic_loss_fwd(value, old_value, target_value, loss_mask, float(value_eps_clip), kind, 10.0)
+    stat = dict(clip_mask=out[4].detach().view(torch.bool), loss=out[3].detach())
+    return out[0], stat
+
+
+@torch.no_grad()
+def get_packed_rewards(
+    kl_ctl: float,
+    clip_reward_value: float,
+    log_probs: torch.Tensor,
+    ref_log_probs: torch.Tensor,
+    reward_score: torch.Tensor,
+    short1cu_seqlens: torch.Tensor,
+    seq_no_eos_mask: torch.Tensor,
+    mask_no_eos_with_zero: bool = False,
+) -> Tuple[torch.Tensor, torch.Tensor]:
+    """KL-shaped token rewards plus the clipped sequence score on each last token
+    (ref ppo_functional.py:228-253). Returns ``(kl_rewards, tot_rewards)``."""
+    kl, tot = ops.packed_rewards(log_probs, ref_log_probs, reward_score, short1cu_seqlens,
+                                 seq_no_eos_mask, float(kl_ctl), float(clip_reward_value),
+                                 bool(mask_no_eos_with_zero))
+    return kl, tot

@@ -179,6 +179,30 @@ int b200rl_ppo_loss_bwd(const float* dlogp, const float* grad_loss, const float*
                         float* g_logp, int64_t T, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Companions of the GAE path in the legacy PPO interface.
+ * ref: realhf/impl/model/utils/ppo_functional.py:150-225 (critic_loss_fn, _mse_loss, _huber_loss),
+ *      :228-253 (get_packed_rewards).
+ *
+ * critic loss: vl = max(f(value, target), f(old + clamp(value-old, -eps, eps), target)), f = mse
+ * (loss_type 0) or huber(huber_delta) (loss_type 1); loss = sum(mask*vl)/count(mask) (no `or 1`,
+ * as in the reference) or mean(vl) when mask is NULL; stat loss/clip_mask; dvalue = d(N*loss)/d value.
+ * The backward of the scalar is b200rl_ppo_loss_bwd (g * dvalue / denom).
+ * packed rewards: kl = tot = -kl_ctl*(log_probs - ref_log_probs); tot[cu[i+1]-1] += clip(score_i)
+ * (0 instead when mask_no_eos_with_zero and seq_no_eos_mask[i]).
+ */
+size_t b200rl_critic_loss_workspace_bytes(int64_t T);
+int b200rl_critic_loss_fwd(const float* value, const float* old_value, const float* target_value,
+                           const uint8_t* mask, int64_t T, float value_eps_clip, int loss_type,
+                           float huber_delta, float* stat_loss, uint8_t* stat_clip_mask,
+                           float* dvalue, float* loss, float* denom, void* workspace,
+                           size_t workspace_bytes, void* stream);
+int b200rl_packed_rewards(const float* log_probs, const float* ref_log_probs,
+                          const float* reward_score, const int32_t* short1cu_seqlens,
+                          const uint8_t* seq_no_eos_mask, int32_t batch, int64_t T, float kl_ctl,
+                          float clip_reward_value, int mask_no_eos_with_zero, float* kl_rewards,
+                          float* tot_rewards, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * H2  masked moments + normalisation (advantage normalisation, batch / group level).
  * ref: areal/utils/functional.py:83-121 (masked_normalization),
  *      areal/engine/ppo/actor.py:412-604 (AdvNorm.__call__, _compute_mean, _compute_std).

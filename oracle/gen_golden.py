@@ -138,6 +138,44 @@ def gen_h2_legacy(P):
         print("wrote h2_legacy", k)
 
 
+def gen_critic_rewards(P):
+    """realhf critic_loss_fn (ppo_functional.py:171-225) and get_packed_rewards (:228-253)."""
+    gen = torch.Generator().manual_seed(21)
+    T = 400
+    for k, (kind, use_mask, eps, spread) in enumerate(
+        [("mse", True, 0.2, 1.0), ("huber", True, 0.5, 12.0), ("mse", False, 0.1, 1.0),
+         ("huber", False, 0.2, 12.0)]
+    ):
+        old = torch.randn(T, generator=gen) * spread
+        value = (old + 0.4 * torch.randn(T, generator=gen)).requires_grad_(True)
+        target = old + torch.randn(T, generator=gen) * spread
+        mask = (torch.rand(T, generator=gen) < 0.7) if use_mask else None
+        loss, stat = P.critic_loss_fn(value, old, target, eps, loss_mask=mask, loss_fn_type=kind)
+        (loss * 1.7).backward()
+        d = dict(value=value.detach().numpy(), old=old.numpy(), target=target.numpy(),
+                 eps=np.float64(eps), huber=np.bool_(kind == "huber"), use_mask=np.bool_(use_mask),
+                 loss=loss.detach().numpy(), g_value=value.grad.numpy(),
+                 stat_loss=stat["loss"].numpy(), stat_clip_mask=stat["clip_mask"].numpy())
+        if use_mask:
+            d["mask"] = mask.numpy()
+        np.savez_compressed(os.path.join(OUT, f"critic_{k}.npz"), **d)
+        print("wrote critic", k)
+    for k, (mz, kl_ctl, clipv) in enumerate([(False, 0.1, 5.0), (True, 0.05, 1.0)]):
+        lens = torch.randint(1, 40, (24,), generator=gen)
+        cu = torch.nn.functional.pad(lens.cumsum(0), (1, 0)).int()
+        Tn = int(cu[-1])
+        lp = -torch.rand(Tn, generator=gen) * 3
+        ref = lp + 0.3 * torch.randn(Tn, generator=gen)
+        score = torch.randn(24, generator=gen) * 3
+        no_eos = torch.rand(24, generator=gen) < 0.3
+        kl, tot = P.get_packed_rewards(kl_ctl, clipv, lp, ref, score, cu, no_eos, mask_no_eos_with_zero=mz)
+        np.savez_compressed(os.path.join(OUT, f"rewards_{k}.npz"), lp=lp.numpy(), ref=ref.numpy(),
+                            score=score.numpy(), cu=cu.numpy(), no_eos=no_eos.numpy(),
+                            kl_ctl=np.float64(kl_ctl), clip=np.float64(clipv), mask_zero=np.bool_(mz),
+                            kl=kl.numpy(), tot=tot.numpy())
+        print("wrote rewards", k)
+
+
 def gen_advnorm(F, AdvNorm):
     class Cfg:
         def __init__(self, m, s, g):
@@ -308,6 +346,7 @@ def main():
     gen_h1(F)
     gen_h2_loss(F)
     gen_h2_legacy(P)
+    gen_critic_rewards(P)
     gen_advnorm(F, R.adv_norm_class())
     gen_gae(P)
     gen_padded_gae()

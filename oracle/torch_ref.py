@@ -237,3 +237,46 @@ def padded_gae(rewards, values, seq_no_eos_mask, gamma, lam):
         last = delta + gamma * lam * last                                       # :145
         rev.append(last)                                                        # :146
     return torch.stack(rev[::-1], dim=1)                                        # :147
+
+
+def critic_loss(value, old_value, target_value, value_eps_clip, loss_mask=None, loss_fn_type="mse"):
+    """Restates realhf/impl/model/utils/ppo_functional.py:150-225 (critic_loss_fn with _mse_loss /
+    _huber_loss, delta = 10). Returns (loss, {clip_mask, loss})."""
+    delta = 10.0
+
+    def f(x, y):
+        if loss_fn_type == "mse":
+            return 0.5 * (x - y) ** 2
+        if loss_fn_type == "huber":
+            diff = torch.abs(x - y)
+            return torch.where(diff < delta, 0.5 * diff**2, delta * (diff - 0.5 * delta))
+        raise NotImplementedError(loss_fn_type)
+
+    orig = f(value, target_value)
+    clipped_value = old_value + (value - old_value).clamp(-value_eps_clip, value_eps_clip)
+    clipped = f(clipped_value, target_value)
+    vl = torch.max(orig, clipped)
+    with torch.no_grad():
+        clip_mask = clipped.detach() > orig.detach()
+        if loss_mask is not None:
+            clip_mask = clip_mask.logical_and(loss_mask)
+        stat = dict(clip_mask=clip_mask, loss=vl.detach())
+    if loss_mask is not None:
+        loss = torch.where(loss_mask, vl, 0).sum() / loss_mask.count_nonzero()
+    else:
+        loss = vl.mean()
+    return loss, stat
+
+
+def packed_rewards(kl_ctl, clip_reward_value, log_probs, ref_log_probs, reward_score,
+                   short1cu_seqlens, seq_no_eos_mask, mask_no_eos_with_zero=False):
+    """Restates realhf/impl/model/utils/ppo_functional.py:228-253 (get_packed_rewards)."""
+    tot = -kl_ctl * (log_probs - ref_log_probs)
+    kl = tot.clone()
+    score = reward_score.clip(-clip_reward_value, clip_reward_value)
+    idx = (short1cu_seqlens[1:] - 1).long()
+    if mask_no_eos_with_zero:
+        tot[idx] += torch.where(seq_no_eos_mask, 0, score)
+    else:
+        tot[idx] += score
+    return kl, tot

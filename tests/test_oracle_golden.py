@@ -142,3 +142,29 @@ def test_padded_gae_vs_reference_loop():
         out = torch_ref.padded_gae(torch.from_numpy(g[f"rewards_{k}"]), torch.from_numpy(g[f"values_{k}"]),
                                    torch.from_numpy(g[f"no_eos_{k}"]), float(g[f"gamma_{k}"]), float(g[f"lam_{k}"]))
         assert np.array_equal(out.numpy(), g[f"adv_{k}"])
+
+
+@pytest.mark.parametrize("k", range(4))
+def test_critic_loss_golden(k):
+    g = load_golden(f"critic_{k}")
+    value = torch.from_numpy(g["value"]).requires_grad_(True)
+    mask = torch.from_numpy(g["mask"]) if bool(g["use_mask"]) else None
+    loss, stat = torch_ref.critic_loss(value, torch.from_numpy(g["old"]), torch.from_numpy(g["target"]),
+                                       float(g["eps"]), loss_mask=mask,
+                                       loss_fn_type="huber" if bool(g["huber"]) else "mse")
+    (loss * 1.7).backward()
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-6)
+    np.testing.assert_allclose(value.grad.numpy(), g["g_value"], rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(stat["loss"].numpy(), g["stat_loss"], rtol=1e-6)
+    assert np.array_equal(stat["clip_mask"].numpy(), g["stat_clip_mask"])
+
+
+@pytest.mark.parametrize("k", range(2))
+def test_packed_rewards_golden(k):
+    g = load_golden(f"rewards_{k}")
+    kl, tot = torch_ref.packed_rewards(float(g["kl_ctl"]), float(g["clip"]), torch.from_numpy(g["lp"]),
+                                       torch.from_numpy(g["ref"]), torch.from_numpy(g["score"]),
+                                       torch.from_numpy(g["cu"]), torch.from_numpy(g["no_eos"]),
+                                       bool(g["mask_zero"]))
+    assert np.array_equal(kl.numpy(), g["kl"])
+    assert np.array_equal(tot.numpy(), g["tot"])
