@@ -1,0 +1,68 @@
+"""Drop-in for the loss function of ``areal/engine/sft/lm_engine.py`` (the SFT twin of
+``grpo_loss_fn``): ``compute_packed_sft_loss(logits, input_)``.
+
+Reference (lm_engine.py:45-86): gather_logprobs over the rolled input ids, masked mean of -logp,
+a python loop over ``cu_seqlens`` for the per-sequence mean log-prob (one host sync per slice
+bound), and two more full passes over ``[T, V]`` for ``logits.min(-1)`` / ``max(-1)``.
+Here: one streaming pass over the logits yields logp AND the row min/max; one small launch yields
+the loss, per-sequence log-prob / perplexity and the gradient seed. No host sync.
+"""
+
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from . import ops
+from .functional import _as_2d
+
+
+def _stats_tracker():
+    try:  # the reference's tracker, when this module is used inside AReaL
+        from areal.utils import stats_tracker  # type: ignore
+
+        return stats_tracker
+    except Exception:
+        return None
+
+
+def compute_packed_sft_loss(logits: torch.Tensor, input_: Dict, stats: Optional[Dict] = None) -> torch.Tensor:
+    """ref areal/engine/sft/lm_engine.py:45-86. ``stats`` (extension): when a dict is passed the
+    logged tensors are also stored there (ppl, loss, vocab_min_logits, vocab_max_logits, seqlogp,
+    n_valid_tokens); inside AReaL they are registered with ``stats_tracker`` under the
+    reference's keys and denominators."""
+    packed_input_ids: torch.Tensor = input_["input_ids"]
+    cu_seqlens: torch.Tensor = input_["cu_seqlens"]
+    loss_mask = input_["loss_mask"].bool()
+
+    labels = torch.roll(packed_input_ids, shifts=-1, dims=-1)
+    loss_mask = torch.roll(loss_mask, shifts=-1, dims=-1)
+    l2, y, lead = _as_2d(logits, labels)
+    logp, _, _, vmax, vmin = ops.logprob_entropy_fwd(l2, y, 1.0, False, True)
+    out = ops.sft_loss_fwd(logp.view(-1), loss_mask.reshape(-1), cu_seqlens)
+    loss = out[0]
+    with torch.no_grad():
+        collected = dict(
+            ppl=out[5].detach(),
+            loss=-out[3].detach().view(lead),
+            vocab_min_logits=vmin.detach().view(lead),
+            vocab_max_logits=vmax.detach().view(lead),
+            seqlogp=out[4].detach(),
+            n_valid_tokens=loss_mask,
+        )
+        if stats is not None:
+            stats.update(collected)
+        st = _stats_tracker()
+        if st is not None:
+            st.denominator(
+                n_seqs=torch.ones(cu_seqlens.shape[0] - 1, dtype=torch.bool, device=logits.device),
+                n_tokens=torch.ones(logits.shape[0], dtype=torch.bool, device=logits.device),
+                n_valid_tokens=loss_mask,
+                prompt_tokens=loss_mask.logical_not(),
+            )
+            st.stat(ppl=collected["ppl"], denominator="n_seqs")
+            st.stat(loss=collected["loss"], denominator="n_valid_tokens")
+            st.stat(vocab_min_logits=collected["vocab_min_logits"],
+                    vocab_max_logits=collected["vocab_max_logits"], denominator="n_tokens")
+    return loss

@@ -598,6 +598,82 @@ def packed_rewards(*args):
 
 
 # --------------------------------------------------------------------------------------------
+# packed SFT loss tail
+# --------------------------------------------------------------------------------------------
+def _raw_sft_loss_fwd(logp: Tensor, mask: Tensor, cu_seqlens: Tensor) -> List[Tensor]:
+    """-> [loss(0-d), denom(1), dlogp, masked_logp, seqlogp(f64 [B]), ppl(f32 [B])]"""
+    _lib.require_cuda(logprobs=logp, loss_mask=mask, cu_seqlens=cu_seqlens)
+    if logp.dim() != 1 or mask.shape != logp.shape:
+        raise RuntimeError("logprobs and loss_mask must be 1-D and of the same length")
+    if logp.dtype != torch.float32:
+        raise RuntimeError(f"logprobs must be float32, got {logp.dtype}")
+    if cu_seqlens.dtype not in (torch.int32, torch.int64) or cu_seqlens.dim() != 1:
+        raise RuntimeError("cu_seqlens must be a 1-D int32 or int64 tensor")
+    dev = logp.device
+    lp = logp.detach().contiguous()
+    mk = (mask if mask.dtype == torch.bool else mask != 0).contiguous().view(torch.uint8)
+    cu = cu_seqlens.contiguous()
+    T, B = lp.numel(), max(cu.numel() - 1, 0)
+    loss = torch.empty((), dtype=torch.float32, device=dev)
+    denom = torch.empty(1, dtype=torch.float32, device=dev)
+    dlogp, masked = torch.empty_like(lp), torch.empty_like(lp)
+    seqlogp = torch.empty(B, dtype=torch.float64, device=dev)
+    ppl = torch.empty(B, dtype=torch.float32, device=dev)
+    ws = _lib.workspace(lib.b200rl_sft_loss_workspace_bytes(T, B), dev)
+    with _on(dev):
+        rc = lib.b200rl_sft_loss_fwd(ptr(lp), ptr(mk), ptr(cu), int(cu.dtype == torch.int64), T, B,
+                                     ptr(masked), ptr(dlogp), ptr(seqlogp), ptr(ppl), ptr(loss),
+                                     ptr(denom), ptr(ws), ws.numel(), stream_handle(dev))
+    check(rc, "b200rl_sft_loss_fwd")
+    return [loss, denom, dlogp, masked, seqlogp, ppl]
+
+
+sft_loss_fwd_op = torch.library.custom_op("b200rl::sft_loss_fwd", _raw_sft_loss_fwd, mutates_args=())
+
+
+@sft_loss_fwd_op.register_fake
+def _(logp, mask, cu_seqlens):
+    B = max(cu_seqlens.shape[0] - 1, 0)
+    return [logp.new_empty((), dtype=torch.float32), logp.new_empty((1,), dtype=torch.float32),
+            torch.empty_like(logp), torch.empty_like(logp), logp.new_empty((B,), dtype=torch.float64),
+            logp.new_empty((B,), dtype=torch.float32)]
+
+
+def _sft_backward(ctx, grads):
+    dlogp, denom = ctx.saved_tensors
+    g = None if grads[0] is None else ppo_loss_bwd_op(dlogp, grads[0], denom)
+    return g, None, None
+
+
+sft_loss_fwd_op.register_autograd(
+    _sft_backward, setup_context=lambda ctx, inputs, output: ctx.save_for_backward(output[2], output[1]))
+
+
+class _SftLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logp, mask, cu_seqlens):
+        out = _raw_sft_loss_fwd(logp, mask, cu_seqlens)
+        ctx.save_for_backward(out[2], out[1])
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(*out[1:])
+        return tuple(out)
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        dlogp, denom = ctx.saved_tensors
+        g = None if g_loss is None else _raw_ppo_loss_bwd(dlogp, g_loss, denom)
+        return g, None, None
+
+
+def sft_loss_fwd(logp, mask, cu_seqlens):
+    if not _eager():
+        return sft_loss_fwd_op(logp, mask, cu_seqlens)
+    if logp.requires_grad and torch.is_grad_enabled():
+        return list(_SftLossFn.apply(logp, mask, cu_seqlens))
+    return _raw_sft_loss_fwd(logp, mask, cu_seqlens)
+
+
+# --------------------------------------------------------------------------------------------
 # H2 masked moments / normalisation
 # --------------------------------------------------------------------------------------------
 def _raw_masked_moments(

@@ -203,6 +203,21 @@ int b200rl_packed_rewards(const float* log_probs, const float* ref_log_probs,
                           float* tot_rewards, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Packed SFT loss tail (the SFT twin of grpo_loss_fn).
+ * ref: areal/engine/sft/lm_engine.py:45-61 (compute_packed_sft_loss).
+ * loss = -sum(mask ? logp : 0) / count(mask) (no `or 1`); masked_logp[t] = mask ? logp : 0;
+ * dlogp[t] = mask ? -1 : 0 (= d(N*loss)/d logp; backward is b200rl_ppo_loss_bwd); per sequence
+ * i over [cu[i], cu[i+1]): seqlogp[i] = (double)(float mean of the valid log-probs), nan when the
+ * sequence has none; ppl[i] = exp(-seqlogp[i]). cu_seqlens is int32, or int64 when cu_is_int64.
+ * masked_logp, dlogp, seqlogp, ppl are nullable.
+ */
+size_t b200rl_sft_loss_workspace_bytes(int64_t T, int64_t batch);
+int b200rl_sft_loss_fwd(const float* logp, const uint8_t* mask, const void* cu_seqlens,
+                        int cu_is_int64, int64_t T, int32_t batch, float* masked_logp, float* dlogp,
+                        double* seqlogp, float* ppl, float* loss, float* denom, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * H2  masked moments + normalisation (advantage normalisation, batch / group level).
  * ref: areal/utils/functional.py:83-121 (masked_normalization),
  *      areal/engine/ppo/actor.py:412-604 (AdvNorm.__call__, _compute_mean, _compute_std).

@@ -176,6 +176,43 @@ def gen_critic_rewards(P):
         print("wrote rewards", k)
 
 
+def gen_sft():
+    """compute_packed_sft_loss (lm_engine.py:45-86) incl. what it registers with stats_tracker."""
+    fn, rec = R.sft_loss_fn()
+    gen = torch.Generator().manual_seed(31)
+    for k, (B, V, dtype, cu_dtype) in enumerate(
+        [(6, 1024, torch.bfloat16, torch.int32), (5, 777, torch.float32, torch.int64)]
+    ):
+        lens = torch.randint(4, 60, (B,), generator=gen)
+        cu = torch.nn.functional.pad(lens.cumsum(0), (1, 0)).to(cu_dtype)
+        T = int(cu[-1])
+        logits, nxt = make_logits(gen, T, V, dtype)
+        logits.requires_grad_(True)
+        ids = torch.roll(nxt, 1)  # so that roll(ids, -1) hits the peaked columns
+        mask = torch.zeros(T, dtype=torch.int32)
+        for i in range(B):  # prompt tokens masked out, like an SFT batch
+            p = int(torch.randint(1, int(lens[i]) - 1, (1,), generator=gen))
+            mask[int(cu[i]) + p: int(cu[i + 1])] = 1
+        loss = fn(logits, dict(input_ids=ids, cu_seqlens=cu, loss_mask=mask))
+        (loss * 2.5).backward()
+        d = dict(input_ids=ids.numpy(), cu=cu.numpy(), loss_mask=mask.numpy(),
+                 loss=loss.detach().numpy())
+        if dtype == torch.float32:
+            d["logits_f32"] = logits.detach().numpy()
+            d["dlogits_f32"] = logits.grad.numpy()
+        else:
+            d["logits_bits"] = bits(logits.detach())
+            d["dlogits_bits"] = bits(logits.grad)
+            d["dtype"] = np.str_("bf16")
+        for key, (v, den) in rec.stats.items():
+            d["stat_" + key] = v.detach().numpy()
+            d["den_" + key] = np.array(den)
+        for key, v in rec.denominators.items():
+            d["denom_" + key] = v.detach().numpy()
+        np.savez_compressed(os.path.join(OUT, f"sft_{k}.npz"), **d)
+        print("wrote sft", k, float(loss.detach()))
+
+
 def gen_advnorm(F, AdvNorm):
     class Cfg:
         def __init__(self, m, s, g):
@@ -347,6 +384,7 @@ def main():
     gen_h2_loss(F)
     gen_h2_legacy(P)
     gen_critic_rewards(P)
+    gen_sft()
     gen_advnorm(F, R.adv_norm_class())
     gen_gae(P)
     gen_padded_gae()

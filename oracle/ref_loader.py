@@ -98,6 +98,35 @@ def adv_norm_class():
     return g["AdvNorm"]
 
 
+class _StatsRecorder:
+    """Stands in for areal.utils.stats_tracker: records what the reference registers."""
+
+    def __init__(self):
+        self.denominators, self.stats = {}, {}
+
+    def denominator(self, **kw):
+        self.denominators.update(kw)
+
+    def stat(self, denominator=None, **kw):
+        for k, v in kw.items():
+            self.stats[k] = (v, denominator)
+
+
+def sft_loss_fn():
+    """compute_packed_sft_loss (areal/engine/sft/lm_engine.py:45-86) bound to the real
+    gather_logprobs and a recording stats tracker. Returns (fn, recorder)."""
+    import torch
+
+    F = areal_functional()
+    rec = _StatsRecorder()
+    g = _extract(
+        os.path.join(REF_ROOT, "areal/engine/sft/lm_engine.py"),
+        {"compute_packed_sft_loss"},
+        dict(torch=torch, TensorDict=dict, gather_logprobs=F.gather_logprobs, stats_tracker=rec),
+    )
+    return g["compute_packed_sft_loss"], rec
+
+
 def merge_intervals_ext():
     """The reference's own merge_intervals, compiled by oracle/Makefile into oracle/_ref/."""
     here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")

@@ -280,3 +280,24 @@ def packed_rewards(kl_ctl, clip_reward_value, log_probs, ref_log_probs, reward_s
     else:
         tot[idx] += score
     return kl, tot
+
+
+def packed_sft_loss(logits, input_ids, cu_seqlens, loss_mask):
+    """Restates areal/engine/sft/lm_engine.py:45-86 (compute_packed_sft_loss) without the stats
+    tracker: returns (loss, dict(seqlogp f64, ppl f32, loss per token, vocab_min/max_logits))."""
+    labels = torch.roll(input_ids, shifts=-1, dims=-1)
+    lp = torch.nn.functional.log_softmax(logits.float(), dim=-1).gather(-1, labels.unsqueeze(-1)).squeeze(-1)
+    m = torch.roll(loss_mask.bool(), shifts=-1, dims=-1)
+    lp = torch.where(m, lp, 0)
+    loss = -lp.sum() / m.count_nonzero()
+    with torch.no_grad():
+        B = cu_seqlens.shape[0] - 1
+        seqlogp = torch.zeros(B, dtype=torch.float64)
+        for i in range(B):
+            mi = m[cu_seqlens[i]: cu_seqlens[i + 1]]
+            li = lp[cu_seqlens[i]: cu_seqlens[i + 1]]
+            seqlogp[i] = torch.where(mi, li.detach(), 0.0).sum() / mi.count_nonzero()
+        stat = dict(seqlogp=seqlogp, ppl=(-seqlogp).exp().float(), loss=-lp.detach(),
+                    vocab_min_logits=logits.detach().min(-1).values.float(),
+                    vocab_max_logits=logits.detach().max(-1).values.float())
+    return loss, stat

@@ -168,3 +168,20 @@ def test_packed_rewards_golden(k):
                                        bool(g["mask_zero"]))
     assert np.array_equal(kl.numpy(), g["kl"])
     assert np.array_equal(tot.numpy(), g["tot"])
+
+
+@pytest.mark.parametrize("k", range(2))
+def test_sft_loss_golden(k):
+    g = load_golden(f"sft_{k}")
+    logits, dref = golden_logits(g)
+    x = logits.clone().requires_grad_(True)
+    loss, stat = torch_ref.packed_sft_loss(x, torch.from_numpy(g["input_ids"]), torch.from_numpy(g["cu"]),
+                                           torch.from_numpy(g["loss_mask"]))
+    (loss * 2.5).backward()
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-6)
+    tol = 1e-6 if logits.dtype == torch.float32 else 8e-3
+    np.testing.assert_allclose(x.grad.float().numpy(), dref.float().numpy(), rtol=tol, atol=1e-8)
+    np.testing.assert_allclose(stat["ppl"].numpy(), g["stat_ppl"], rtol=1e-5)
+    np.testing.assert_allclose(stat["loss"].numpy(), g["stat_loss"], rtol=1e-6, atol=1e-7)
+    assert np.array_equal(stat["vocab_min_logits"].numpy(), g["stat_vocab_min_logits"])
+    assert np.array_equal(stat["vocab_max_logits"].numpy(), g["stat_vocab_max_logits"])
