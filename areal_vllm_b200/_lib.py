@@ -86,6 +86,14 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_float, c_float, c_int,
          c_void_p, c_void_p, c_void_p],
     ),
+    "b200rl_logprob_shard_fwd": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_void_p, c_int64, c_int64, c_float, c_int, c_int, c_void_p, c_void_p],
+    ),
+    "b200rl_logprob_shard_combine": (
+        c_int,
+        [c_void_p, c_int32, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
     "b200rl_sft_loss_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "b200rl_sft_loss_fwd": (
         c_int,

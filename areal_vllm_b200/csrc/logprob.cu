@@ -27,6 +27,9 @@ namespace {
 
 using namespace lp;
 
+// floats per row of the vocabulary-shard partial record: (M, S, W, x_y, max, min, 0, 0)
+constexpr int kPartialStride = 8;
+
 // ------------------------------------------------------------------------------------------
 // forward, rows 16-B aligned (bf16 / fp16 / fp32)
 // ------------------------------------------------------------------------------------------
@@ -36,7 +39,7 @@ logprob_fwd_kernel(const void* __restrict__ logits, int64_t ld,
                         const int64_t* __restrict__ labels, int T, int V, float scale,
                         float* __restrict__ logp, float* __restrict__ ent,
                         float* __restrict__ lse, float* __restrict__ rowmax,
-                        float* __restrict__ rowmin) {
+                        float* __restrict__ rowmin, float* __restrict__ partial) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FwdSmem<WARPS, STAGES>;
   using E = Elem<DT>;
@@ -159,15 +162,22 @@ logprob_fwd_kernel(const void* __restrict__ logits, int64_t ld,
       }
       if (lane == 0) {
         cnt[slot] = 0;
-        const float l2s = log2f(Sr);
-        lse[row] = (Mr + l2s) * kLn2;
-        // (x_y*scale - M) first: exact cancellation when the label is the row maximum, however
-        // large |M| is; only then the (small) log2 of the sum
-        logp[row] = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
-        if (ENT) ent[row] = kLn2 * (l2s - Tr / Sr);
-        if (MINMAX) {
-          if (rowmax) rowmax[row] = mxr;
-          if (rowmin) rowmin[row] = mnr;
+        if (partial) {
+          // vocabulary-shard mode: raw online-softmax state of this shard's slice of the row
+          float4* pr = reinterpret_cast<float4*>(partial + (int64_t)row * kPartialStride);
+          pr[0] = make_float4(Mr, Sr, Tr, xyr);
+          pr[1] = make_float4(mxr, mnr, 0.f, 0.f);
+        } else {
+          const float l2s = log2f(Sr);
+          lse[row] = (Mr + l2s) * kLn2;
+          // (x_y*scale - M) first: exact cancellation when the label is the row maximum, however
+          // large |M| is; only then the (small) log2 of the sum
+          logp[row] = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
+          if (ENT) ent[row] = kLn2 * (l2s - Tr / Sr);
+          if (MINMAX) {
+            if (rowmax) rowmax[row] = mxr;
+            if (rowmin) rowmin[row] = mnr;
+          }
         }
         __threadfence_block();
         gen[slot] = use + 1;
@@ -287,7 +297,7 @@ __global__ void __launch_bounds__(kPlainThreads)
 logprob_fwd_plain_kernel(const T* __restrict__ logits, int64_t ld, const int64_t* __restrict__ labels,
                          int64_t V, float scale, float* __restrict__ logp, float* __restrict__ ent,
                          float* __restrict__ lse, float* __restrict__ rowmax,
-                         float* __restrict__ rowmin) {
+                         float* __restrict__ rowmin, float* __restrict__ partial) {
   __shared__ float sh[kPlainThreads / 32];
   const int64_t row = blockIdx.x;
   const T* x = logits + row * ld;
@@ -314,6 +324,12 @@ logprob_fwd_plain_kernel(const T* __restrict__ logits, int64_t ld, const int64_t
     const float lse2 = m2 + l2s;
     const int64_t lab = labels[row];
     const float xy = (lab >= 0 && lab < V) ? to_f<T>(x[lab]) : __int_as_float(0x7fc00000);
+    if (partial) {
+      float4* pr = reinterpret_cast<float4*>(partial + row * kPartialStride);
+      pr[0] = make_float4(m2, s, t, xy);
+      pr[1] = make_float4(mx, mn, 0.f, 0.f);
+      return;
+    }
     lse[row] = lse2 * kLn2;
     logp[row] = (fmaf(xy, scale, -m2) - l2s) * kLn2;
     if (ent) ent[row] = kLn2 * (l2s - t / s);
@@ -393,30 +409,64 @@ static_assert(FwdSmem<kFwdWarps, kFwdStages>::kBytes <= 227 * 1024, "forward rin
 static_assert(FwdSmem<kBwdWarps, kBwdStages>::kBytes <= 227 * 1024, "backward ring exceeds shared memory");
 static_assert(kFwdWarps <= 32, "the finalising warp reads one partial per lane");
 
+// ------------------------------------------------------------------------------------------
+// vocabulary-parallel combine: one thread per row folds the n_shards partial records
+// (after the tensor-parallel all-gather) with the same algebra the warps use inside a row.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+logprob_shard_combine_kernel(const float* __restrict__ partials, int n_shards, int64_t T, float scale,
+                             float* __restrict__ logp, float* __restrict__ ent,
+                             float* __restrict__ lse, float* __restrict__ rowmax,
+                             float* __restrict__ rowmin) {
+  const int64_t row = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (row >= T) return;
+  const float4* base = reinterpret_cast<const float4*>(partials);
+  float M = -INFINITY;
+  for (int k = 0; k < n_shards; k++) M = fmaxf(M, base[((int64_t)k * T + row) * 2].x);
+  float S = 0.f, W = 0.f, xy = __int_as_float(0x7fc00000), mx = -INFINITY, mn = INFINITY;
+  for (int k = 0; k < n_shards; k++) {
+    const float4 a = base[((int64_t)k * T + row) * 2];
+    const float4 b = base[((int64_t)k * T + row) * 2 + 1];
+    const float d = a.x - M;  // <= 0
+    const float f = ex2_approx(d);
+    S = fmaf(a.y, f, S);
+    W = fmaf(f, fmaf(d, a.y, a.z), W);
+    if (a.w == a.w) xy = a.w;  // the one shard that owns the label column
+    mx = fmaxf(mx, b.x);
+    mn = fminf(mn, b.y);
+  }
+  const float l2s = log2f(S);
+  lse[row] = (M + l2s) * kLn2;
+  logp[row] = (fmaf(xy, scale, -M) - l2s) * kLn2;
+  if (ent) ent[row] = kLn2 * (l2s - W / S);
+  if (rowmax) rowmax[row] = mx;
+  if (rowmin) rowmin[row] = mn;
+}
+
 template <int DT, bool ENT, bool MINMAX>
 int launch_fwd_fast(const void* logits, int64_t ld, const int64_t* labels, int T, int V,
                     float scale, float* logp, float* ent, float* lse, float* rowmax,
-                    float* rowmin, cudaStream_t st) {
+                    float* rowmin, float* partial, cudaStream_t st) {
   auto k = logprob_fwd_kernel<DT, kFwdWarps, kFwdStages, ENT, MINMAX>;
   constexpr int smem = FwdSmem<kFwdWarps, kFwdStages>::kBytes;
   int rc = set_smem(k, smem);
   if (rc) return rc;
   const int grid = min(T, sm_count());
-  k<<<grid, kFwdWarps * 32, smem, st>>>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin);
+  k<<<grid, kFwdWarps * 32, smem, st>>>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin,
+                                        partial);
   return check_launch("logprob_fwd_kernel");
 }
 
 template <int DT>
 int dispatch_fwd_fast(const void* logits, int64_t ld, const int64_t* labels, int T, int V,
                       float scale, float* logp, float* ent, float* lse, float* rowmax,
-                      float* rowmin, cudaStream_t st) {
-  const bool mm = rowmax != nullptr || rowmin != nullptr;
-  if (ent) {
-    return mm ? launch_fwd_fast<DT, true, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st)
-              : launch_fwd_fast<DT, true, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st);
+                      float* rowmin, float* partial, bool want_ent, bool want_mm, cudaStream_t st) {
+  if (want_ent) {
+    return want_mm ? launch_fwd_fast<DT, true, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st)
+                   : launch_fwd_fast<DT, true, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st);
   }
-  return mm ? launch_fwd_fast<DT, false, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st)
-            : launch_fwd_fast<DT, false, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, st);
+  return want_mm ? launch_fwd_fast<DT, false, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st)
+                 : launch_fwd_fast<DT, false, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st);
 }
 
 template <int DT, bool HAS_GH>
@@ -448,19 +498,20 @@ inline int per_vec(int dtype) { return dtype == B200RL_FP32 ? 4 : 8; }
 }  // namespace
 }  // namespace b200rl
 
-extern "C" {
-
-int b200rl_logprob_entropy_fwd(const void* logits, int dtype, int64_t ld, const int64_t* labels,
-                               int64_t T, int64_t V, float temperature, float* logp,
-                               float* entropy, float* lse, float* rowmax, float* rowmin,
-                               void* stream) {
+// shared by the whole-vocabulary forward and the vocabulary-shard (partial) forward
+static int logprob_fwd_impl(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                            int64_t T, int64_t V, float temperature, float* logp, float* entropy,
+                            float* lse, float* rowmax, float* rowmin, float* partial, bool want_ent,
+                            bool want_mm, void* stream) {
   using namespace b200rl;
   B200RL_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
   B200RL_REQUIRE(ld >= V, "row stride %lld < V %lld", (long long)ld, (long long)V);
   B200RL_REQUIRE(temperature > 0.f, "temperature must be > 0, got %f", temperature);
   B200RL_REQUIRE(T < INT32_MAX && V < INT32_MAX, "T and V must fit int32");
   if (T == 0) return B200RL_OK;
-  B200RL_REQUIRE(logits && labels && logp && lse, "null pointer");
+  B200RL_REQUIRE(logits && labels && (partial || (logp && lse)), "null pointer");
+  B200RL_REQUIRE(!partial || (reinterpret_cast<uintptr_t>(partial) % 16 == 0),
+                 "partial buffer must be 16-B aligned");
   cudaStream_t st = (cudaStream_t)stream;
   const float scale = (float)(1.4426950408889634 / (double)temperature);
   B200RL_REQUIRE(dtype == B200RL_BF16 || dtype == B200RL_FP16 || dtype == B200RL_FP32,
@@ -470,32 +521,69 @@ int b200rl_logprob_entropy_fwd(const void* logits, int dtype, int64_t ld, const 
   if (fast) {
     switch (dtype) {
       case B200RL_BF16:
-        return dispatch_fwd_fast<B200RL_BF16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, st);
+        return dispatch_fwd_fast<B200RL_BF16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, st);
       case B200RL_FP16:
-        return dispatch_fwd_fast<B200RL_FP16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, st);
+        return dispatch_fwd_fast<B200RL_FP16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, st);
       default:
-        return dispatch_fwd_fast<B200RL_FP32>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, st);
+        return dispatch_fwd_fast<B200RL_FP32>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, st);
     }
   }
   const unsigned grid = (unsigned)T;
   switch (dtype) {
     case B200RL_BF16:
       logprob_fwd_plain_kernel<__nv_bfloat16><<<grid, kPlainThreads, 0, st>>>(
-          (const __nv_bfloat16*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin);
+          (const __nv_bfloat16*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial);
       break;
     case B200RL_FP16:
       logprob_fwd_plain_kernel<__half><<<grid, kPlainThreads, 0, st>>>(
-          (const __half*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin);
+          (const __half*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial);
       break;
     case B200RL_FP32:
       logprob_fwd_plain_kernel<float><<<grid, kPlainThreads, 0, st>>>(
-          (const float*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin);
+          (const float*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial);
       break;
     default:
       set_last_error("unsupported logits dtype code %d", dtype);
       return B200RL_EUNSUPPORTED;
   }
   return check_launch("logprob_fwd_plain_kernel");
+}
+
+extern "C" {
+
+int b200rl_logprob_entropy_fwd(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                               int64_t T, int64_t V, float temperature, float* logp,
+                               float* entropy, float* lse, float* rowmax, float* rowmin,
+                               void* stream) {
+  return logprob_fwd_impl(logits, dtype, ld, labels, T, V, temperature, logp, entropy, lse, rowmax,
+                          rowmin, nullptr, entropy != nullptr, rowmax != nullptr || rowmin != nullptr,
+                          stream);
+}
+
+int b200rl_logprob_shard_fwd(const void* logits, int dtype, int64_t ld, const int64_t* local_labels,
+                             int64_t T, int64_t V_shard, float temperature, int need_entropy,
+                             int need_minmax, float* partial, void* stream) {
+  using namespace b200rl;
+  B200RL_REQUIRE(partial || T == 0, "partial must not be null");
+  return logprob_fwd_impl(logits, dtype, ld, local_labels, T, V_shard, temperature, nullptr, nullptr,
+                          nullptr, nullptr, nullptr, partial, need_entropy != 0, need_minmax != 0,
+                          stream);
+}
+
+int b200rl_logprob_shard_combine(const float* partials, int32_t n_shards, int64_t T,
+                                 float temperature, float* logp, float* entropy, float* lse,
+                                 float* rowmax, float* rowmin, void* stream) {
+  using namespace b200rl;
+  B200RL_REQUIRE(T >= 0 && n_shards >= 1, "bad shape T=%lld n_shards=%d", (long long)T, n_shards);
+  B200RL_REQUIRE(temperature > 0.f, "temperature must be > 0, got %f", temperature);
+  if (T == 0) return B200RL_OK;
+  B200RL_REQUIRE(partials && logp && lse, "null pointer");
+  B200RL_REQUIRE(reinterpret_cast<uintptr_t>(partials) % 16 == 0, "partials must be 16-B aligned");
+  const float scale = (float)(1.4426950408889634 / (double)temperature);
+  const unsigned grid = (unsigned)((T + 255) / 256);
+  logprob_shard_combine_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      partials, n_shards, T, scale, logp, entropy, lse, rowmax, rowmin);
+  return check_launch("logprob_shard_combine_kernel");
 }
 
 int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const int64_t* labels,

@@ -191,6 +191,52 @@ def logprob_entropy_bwd(logits, labels, lse, entropy, g_logp, g_ent, temperature
 
 
 # --------------------------------------------------------------------------------------------
+# H1 over a vocabulary-parallel shard: partial records + combine
+# --------------------------------------------------------------------------------------------
+PARTIAL_STRIDE = 8  # floats per row: (M, S, W, x_y, max, min, 0, 0)
+
+
+def _raw_logprob_shard_fwd(logits: Tensor, local_labels: Tensor, temperature: float,
+                           need_entropy: bool, need_minmax: bool) -> Tensor:
+    """-> partial [T, 8] fp32 for this rank's [T, V_shard] slice (labels already shifted by the
+    shard's first column; out-of-shard labels are fine)."""
+    _check_logits(logits, local_labels)
+    T, V = logits.shape
+    dev = logits.device
+    partial = torch.empty(T, PARTIAL_STRIDE, dtype=torch.float32, device=dev)
+    with _on(dev):
+        rc = lib.b200rl_logprob_shard_fwd(
+            ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
+            ptr(local_labels), T, V, float(temperature), int(need_entropy), int(need_minmax),
+            ptr(partial), stream_handle(dev))
+    check(rc, "b200rl_logprob_shard_fwd")
+    return partial
+
+
+def _raw_logprob_shard_combine(partials: Tensor, temperature: float, need_entropy: bool,
+                               need_minmax: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """partials [n_shards, T, 8] -> (logp, entropy or empty, lse, rowmax or empty, rowmin or empty)."""
+    _lib.require_cuda(partials=partials)
+    if partials.dim() != 3 or partials.shape[2] != PARTIAL_STRIDE or partials.dtype != torch.float32:
+        raise RuntimeError(f"partials must be fp32 [n_shards, T, {PARTIAL_STRIDE}], got {tuple(partials.shape)}")
+    partials = partials.contiguous()
+    n, T, _ = partials.shape
+    dev = partials.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    logp, lse = torch.empty(T, **f32), torch.empty(T, **f32)
+    ent = torch.empty(T if need_entropy else 0, **f32)
+    rmax = torch.empty(T if need_minmax else 0, **f32)
+    rmin = torch.empty(T if need_minmax else 0, **f32)
+    with _on(dev):
+        rc = lib.b200rl_logprob_shard_combine(
+            ptr(partials), n, T, float(temperature), ptr(logp), ptr(ent) if need_entropy else None,
+            ptr(lse), ptr(rmax) if need_minmax else None, ptr(rmin) if need_minmax else None,
+            stream_handle(dev))
+    check(rc, "b200rl_logprob_shard_combine")
+    return logp, ent, lse, rmax, rmin
+
+
+# --------------------------------------------------------------------------------------------
 # H1+H2 fused GRPO step (eager only: it allocates and fills dlogits in the forward)
 # --------------------------------------------------------------------------------------------
 def _raw_grpo_fused_step(

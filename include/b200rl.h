@@ -62,6 +62,29 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
                                void* dlogits, int64_t ld_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * H1 over a vocabulary-parallel (tensor-parallel) shard of the logits.
+ * ref: areal/experimental/megatron_actor.py:60-66, 323-331 (logits.float()/T, then
+ *      megatron.core.tensor_parallel.vocab_parallel_cross_entropy and _VocabParallelEntropy) and
+ *      areal/experimental/utils/mcore/functional.py:8-52 (three all-reduces + four passes).
+ *
+ * b200rl_logprob_shard_fwd: one streaming pass over this rank's [T, V_shard] slice writes, per
+ * row, 8 floats to `partial`: (M, S, W, x_y, max, min, 0, 0) - the online-softmax state in the
+ * log2 domain (M = max of x*log2e/T, S = sum 2^(.-M), W = sum 2^(.-M)*(.-M)), the raw label
+ * logit (NaN when `local_labels[t]` = label - vocab_start is outside [0, V_shard)), and the raw
+ * row max / min (need_minmax). After ONE all-gather of the [T, 8] records over the tensor-parallel
+ * group, b200rl_logprob_shard_combine folds `partials` [n_shards, T, 8] into the same outputs as
+ * b200rl_logprob_entropy_fwd (entropy, rowmax, rowmin nullable). The backward needs no exchange:
+ * b200rl_logprob_entropy_bwd on the shard with the global lse / entropy and the local labels
+ * (out-of-range labels add no one-hot term).
+ */
+int b200rl_logprob_shard_fwd(const void* logits, int dtype, int64_t ld, const int64_t* local_labels,
+                             int64_t T, int64_t V_shard, float temperature, int need_entropy,
+                             int need_minmax, float* partial, void* stream);
+int b200rl_logprob_shard_combine(const float* partials, int32_t n_shards, int64_t T,
+                                 float temperature, float* logp, float* entropy, float* lse,
+                                 float* rowmax, float* rowmin, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * H1+H2 fused: the whole GRPO actor step on one packed micro-batch in ONE pass over HBM.
  * ref: areal/engine/ppo/actor.py:292-367 (grpo_loss_fn) followed by loss.backward()
  *      (areal/engine/fsdp_engine.py:542-550).

@@ -1,0 +1,67 @@
+"""Vocabulary-parallel log-prob over a real NCCL group: run under torchrun with N GPUs, e.g.
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+      --master-port 29533 scripts/tp_check.py
+Every rank builds the same full logits, keeps its column shard, and checks the sharded result and
+gradient against the whole-vocabulary kernel run locally. Also times the sharded forward+backward.
+Prints one JSON line on rank 0."""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from areal_vllm_b200 import functional, mcore_functional  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    T, V = (int(sys.argv[1]) if len(sys.argv) > 1 else 4096), 151936
+    assert V % world == 0
+    gen = torch.Generator(device=dev).manual_seed(7)
+    full = (torch.randn(T, V, generator=gen, device=dev) * 2).bfloat16()
+    labels = torch.randint(0, V, (T,), generator=gen, device=dev)
+    g1 = torch.randn(T, generator=gen, device=dev)
+    g2 = torch.randn(T, generator=gen, device=dev) * 0.1
+    Vs = V // world
+    shard = full[:, rank * Vs:(rank + 1) * Vs].contiguous().requires_grad_(True)
+    lp, ent = mcore_functional.vocab_parallel_logprobs_entropy(shard, labels, 0.9, group=dist.group.WORLD)
+    ((lp * g1).sum() + (ent * g2).sum()).backward()
+    ref_in = full.clone().requires_grad_(True)
+    lp_r, ent_r = functional.gather_logprobs_entropy(ref_in, labels, 0.9)
+    ((lp_r * g1).sum() + (ent_r * g2).sum()).backward()
+    err = dict(
+        logp=float((lp.detach() - lp_r.detach()).abs().max()),
+        ent=float((ent.detach() - ent_r.detach()).abs().max()),
+        grad=float((shard.grad.float() - ref_in.grad[:, rank * Vs:(rank + 1) * Vs].float()).abs().max()),
+    )
+    ok = err["logp"] < 2e-5 and err["ent"] < 2e-5 and err["grad"] < 1e-3
+    # timing: sharded fwd+bwd (max over ranks)
+    del ref_in, full
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    for it in range(8):
+        if it == 3:
+            dist.barrier()
+            torch.cuda.synchronize()
+            ev[0].record()
+        shard.grad = None
+        lp, ent = mcore_functional.vocab_parallel_logprobs_entropy(shard, labels, 0.9, group=dist.group.WORLD)
+        ((lp * g1).sum() + (ent * g2).sum()).backward()
+    ev[1].record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([ev[0].elapsed_time(ev[1]) / 5, 0.0 if ok else 1.0], device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(json.dumps(dict(tp=world, T=T, V=V, ok=bool(ms[1].item() == 0), max_abs_err=err,
+                              fwd_bwd_ms=float(ms[0]), tokens_per_s=T / float(ms[0]) * 1e3,
+                              shard_GBps=6 * Vs * T / float(ms[0]) / 1e6)))
+    dist.destroy_process_group()
+    sys.exit(0 if ms[1].item() == 0 else 1)
+
+
+if __name__ == "__main__":
+    main()

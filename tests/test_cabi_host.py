@@ -242,3 +242,109 @@ def test_plumbing_functions_cpu():
         d2 = dict(rewards=torch.tensor([1.0, 1.0]), input_ids=torch.zeros(2, 10), loss_mask=d["loss_mask"])
         ref = F.reward_overlong_penalty(d2, overlong_tokens=4, overlong_penalty_factor=1.0, max_response_length=10)
         np.testing.assert_allclose(out["rewards"].numpy(), ref["rewards"].numpy())
+
+
+def test_new_dropin_signatures_match_live_reference():
+    """critic_loss_fn / get_packed_rewards / compute_packed_sft_loss / Megatron grpo_loss_fn."""
+    from oracle import ref_loader as R
+
+    import areal_vllm_b200 as pkg
+
+    want = {
+        "critic_loss_fn": ["value", "old_value", "target_value", "value_eps_clip", "loss_mask", "loss_fn_type"],
+        "get_packed_rewards": ["kl_ctl", "clip_reward_value", "log_probs", "ref_log_probs", "reward_score",
+                               "short1cu_seqlens", "seq_no_eos_mask", "mask_no_eos_with_zero"],
+    }
+    for name, params in want.items():
+        assert list(inspect.signature(getattr(pkg.ppo_functional, name)).parameters) == params
+    assert list(inspect.signature(pkg.lm_engine.compute_packed_sft_loss).parameters)[:2] == ["logits", "input_"]
+    assert list(inspect.signature(pkg.mcore_functional.grpo_loss_fn).parameters)[:6] == [
+        "logits", "input_data", "temperature", "eps_clip", "c_clip", "behav_imp_weight_cap"]
+    if not R.available():
+        return
+    P = R.realhf_ppo_functional()
+    for name, params in want.items():
+        ref = inspect.signature(getattr(P, name))
+        got = inspect.signature(getattr(pkg.ppo_functional, name))
+        assert list(ref.parameters) == params
+        for k, p in ref.parameters.items():
+            assert got.parameters[k].default == p.default, (name, k)
+
+
+def _np_partial(x, labels, start, scale):
+    """numpy statement of one shard's 8-float record (M, S, W, x_y, max, min, 0, 0)."""
+    z = x.astype(np.float64) * scale
+    M = z.max(-1)
+    e = np.exp2(z - M[:, None])
+    S = e.sum(-1)
+    W = (e * (z - M[:, None])).sum(-1)
+    loc = labels - start
+    own = (loc >= 0) & (loc < x.shape[1])
+    xy = np.where(own, x[np.arange(len(x)), np.clip(loc, 0, x.shape[1] - 1)], np.nan)
+    return np.stack([M, S, W, xy, x.max(-1), x.min(-1), 0 * M, 0 * M], -1).astype(np.float32)
+
+
+def _np_combine(parts, scale):
+    parts = parts.astype(np.float64)
+    M = parts[:, :, 0].max(0)
+    f = np.exp2(parts[:, :, 0] - M)
+    S = (parts[:, :, 1] * f).sum(0)
+    W = (f * ((parts[:, :, 0] - M) * parts[:, :, 1] + parts[:, :, 2])).sum(0)
+    xy = np.nansum(parts[:, :, 3], 0)
+    ln2 = np.log(2.0)
+    return ((xy * scale - M) - np.log2(S)) * ln2, ln2 * (np.log2(S) - W / S)
+
+
+def _tp_worker(rank, world, port, q):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from areal_vllm_b200.mcore_functional import gather_partials, vocab_range
+
+    rng = np.random.default_rng(5)  # same on every rank
+    T, V, temp = 33, 96, 0.7
+    x = (rng.standard_normal((T, V)) * 3).astype(np.float32)
+    labels = rng.integers(0, V, T)
+    s, e = vocab_range(V // world, rank, world)
+    part = torch.from_numpy(_np_partial(x[:, s:e], labels, s, np.log2(np.e) / temp))
+    allp = gather_partials(part, dist.group.WORLD)
+    assert allp.shape == (world, T, 8)
+    assert torch.equal(allp[rank].view(torch.int32), part.view(torch.int32))  # bits: x_y is nan off-shard
+    lp, ent = _np_combine(allp.numpy(), np.log2(np.e) / temp)
+    q.put((rank, (s, e), lp.tolist(), ent.tolist()))
+    dist.destroy_process_group()
+
+
+def test_vocab_parallel_exchange_gloo_world2():
+    """The N>1 host path of the vocabulary-parallel op: shard ranges, label ownership and the one
+    all-gather, with the record algebra restated in numpy and checked against the oracle."""
+    import torch.multiprocessing as mp
+
+    from areal_vllm_b200.mcore_functional import gather_partials, vocab_range
+    from oracle import torch_ref
+
+    assert vocab_range(100, 0, 4) == (0, 100) and vocab_range(100, 3, 4) == (300, 400)
+    with pytest.raises(ValueError):
+        vocab_range(100, 4, 4)
+    one = torch.zeros(5, 8)
+    assert gather_partials(one, None).shape == (1, 5, 8)
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_tp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert res[0][1] == (0, 48) and res[1][1] == (48, 96)
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal((33, 96)) * 3).astype(np.float32)
+    labels = rng.integers(0, 96, 33)
+    lp64, ent64 = torch_ref.logprobs_entropy_f64(torch.from_numpy(x), torch.from_numpy(labels), 0.7)
+    for _, _, lp, ent in res:  # both ranks hold the same full-vocabulary answer
+        np.testing.assert_allclose(lp, lp64.numpy(), rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(ent, ent64.numpy(), rtol=1e-5, atol=1e-6)
