@@ -518,7 +518,8 @@ def main_b200rl(args):
                  "value": fval, "unit": "tokens/s", "ms_per_step": fms / args.steps,
                  "speedup_vs_separate_path": fval / value,
                  "algorithmic_bytes_per_token": 4 * V,
-                 "hbm_GBps_at_4V": fval * 4 * V / 1e9, "frac_of_measured_peak_at_4V": fval * 4 * V / 1e9 / peak,
+                 "hbm_GBps_per_gpu_at_4V": fval / world * 4 * V / 1e9,
+                 "frac_of_measured_peak_at_4V": fval / world * 4 * V / 1e9 / peak,
                  "note": "each row is read from HBM once (forward statistics) and again from L2 for the "
                          "backward; needs the loss scale before backward(), see INTEGRATION.md"}
 
