@@ -94,6 +94,16 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_int32, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "b200rl_move_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int]),
+    "b200rl_move_intervals": (
+        c_int,
+        [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int,
+         c_void_p, c_size_t, c_int, c_void_p],
+    ),
+    "b200rl_enable_peer_access": (c_int, [c_int, c_int]),
+    "b200rl_ipc_export": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "b200rl_ipc_open": (c_int, [c_void_p, c_int, c_void_p]),
+    "b200rl_ipc_close": (c_int, [c_void_p, c_int]),
     "b200rl_sft_loss_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "b200rl_sft_loss_fwd": (
         c_int,

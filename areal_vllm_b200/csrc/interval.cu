@@ -13,6 +13,7 @@
 //
 // Bound: HBM. Algorithmic bytes = 2 * elem_size per copied element (+16 B per interval).
 #include "common.cuh"
+#include <string.h>
 
 namespace b200rl {
 namespace {
@@ -353,6 +354,54 @@ interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
   }
 }
 
+// MOVE: big -> big without the packed staging buffer (the kernel the reference's TODO at
+// real_llm_api.py:719-720 asks for). Two plans over the same virtual packed stream: the source
+// intervals cut it one way, the destination intervals another; a tile walks both lists and moves
+// the intersections. `src` may be peer memory (NVLink loads): nothing here waits on another GPU.
+template <int ES>
+__global__ void __launch_bounds__(kCopyWarps * 32, 4)
+interval_move_kernel(const char* __restrict__ src, char* __restrict__ dst,
+                     const int64_t* __restrict__ s_iv, const int64_t* __restrict__ s_off,
+                     const int32_t* __restrict__ s_first, const int64_t* __restrict__ s_hdr, int64_t s_n,
+                     const int64_t* __restrict__ d_iv, const int64_t* __restrict__ d_off,
+                     const int32_t* __restrict__ d_first, const int64_t* __restrict__ d_hdr, int64_t d_n,
+                     int64_t num_tiles) {
+  const int lane = threadIdx.x & 31;
+  const int64_t tile = (int64_t)blockIdx.x * kCopyWarps + (threadIdx.x >> 5);
+  if (tile >= num_tiles) return;
+  const bool src_ok = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+  int64_t total_elems = s_hdr[0] < d_hdr[0] ? s_hdr[0] : d_hdr[0];
+  if (total_elems > s_hdr[3]) total_elems = s_hdr[3];
+  const int64_t total_bytes = total_elems * ES;
+  int64_t p0 = tile * (int64_t)kTileBytes;
+  int64_t p1 = p0 + kTileBytes;
+  if (p1 > total_bytes) p1 = total_bytes;
+  int64_t i = s_first[tile], j = d_first[tile];
+  int64_t sob = 0, soe = -1, sst = 0, dob = 0, doe = -1, dst_start = 0;
+  while (p0 < p1) {
+    if (soe <= p0) {  // (re)load the source interval covering p0, skipping empty ones
+      if (i >= s_n) break;
+      sob = s_off[i] * ES;
+      soe = s_off[i + 1] * ES;
+      sst = s_iv[2 * i] * ES;
+      i++;
+      continue;
+    }
+    if (doe <= p0) {
+      if (j >= d_n) break;
+      dob = d_off[j] * ES;
+      doe = d_off[j + 1] * ES;
+      dst_start = d_iv[2 * j] * ES;
+      j++;
+      continue;
+    }
+    int64_t b = soe < doe ? soe : doe;
+    if (b > p1) b = p1;
+    copy_piece<ES>(src + sst + (p0 - sob), dst + dst_start + (p0 - dob), b - p0, lane, src_ok);
+    p0 = b;
+  }
+}
+
 int elem_shift_of(int elem_size) {
   switch (elem_size) {
     case 1: return 0;
@@ -415,6 +464,51 @@ int run_copy(const void* src, void* dst, int64_t big_numel, int64_t packed_numel
   return check_launch("interval_copy_kernel");
 }
 
+int run_move(const void* src, int64_t src_numel, void* dst, int64_t dst_numel,
+             const int64_t* s_iv, int64_t s_n, const int64_t* d_iv, int64_t d_n, int64_t total_numel,
+             int elem_size, void* ws, size_t ws_bytes, int reuse_plan, void* stream) {
+  B200RL_REQUIRE(s_n >= 0 && d_n >= 0 && total_numel >= 0 && src_numel >= 0 && dst_numel >= 0, "negative size");
+  const int shift = elem_shift_of(elem_size);
+  B200RL_REQUIRE(shift >= 0, "elem_size %d not in {1,2,4,8}", elem_size);
+  if (total_numel == 0) return B200RL_OK;
+  B200RL_REQUIRE(s_n > 0 && d_n > 0, "total_numel > 0 with an empty interval list");
+  B200RL_REQUIRE(src && dst && s_iv && d_iv && ws, "null pointer");
+  B200RL_REQUIRE(s_n < (int64_t)INT32_MAX && d_n < (int64_t)INT32_MAX, "too many intervals");
+  B200RL_REQUIRE(((reinterpret_cast<uintptr_t>(s_iv) | reinterpret_cast<uintptr_t>(d_iv)) & 15) == 0,
+                 "intervals must be 16-B aligned");
+  B200RL_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "workspace must be 256-B aligned");
+  B200RL_REQUIRE(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & (elem_size - 1)) == 0,
+                 "src/dst must be element aligned");
+  PlanLayout Ls = plan_layout(ws, s_n, total_numel, elem_size);
+  PlanLayout Ld = plan_layout((char*)ws + Ls.bytes, d_n, total_numel, elem_size);
+  if (ws_bytes < Ls.bytes + Ld.bytes) {
+    set_last_error("interval move workspace too small: %zu < %zu", ws_bytes, Ls.bytes + Ld.bytes);
+    return B200RL_EWORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!reuse_plan) {
+    int rc = build_plan(Ls, s_iv, s_n, src_numel, total_numel, shift, st);
+    if (rc) return rc;
+    rc = build_plan(Ld, d_iv, d_n, dst_numel, total_numel, shift, st);
+    if (rc) return rc;
+  }
+  const unsigned grid = (unsigned)((Ls.num_tiles + kCopyWarps - 1) / kCopyWarps);
+  const char* s = (const char*)src;
+  char* d = (char*)dst;
+#define LAUNCH(ES)                                                                                \
+  interval_move_kernel<ES><<<grid, kCopyWarps * 32, 0, st>>>(s, d, s_iv, Ls.offsets, Ls.tile_first, \
+                                                            Ls.hdr, s_n, d_iv, Ld.offsets,        \
+                                                            Ld.tile_first, Ld.hdr, d_n, Ls.num_tiles)
+  switch (elem_size) {
+    case 1: LAUNCH(1); break;
+    case 2: LAUNCH(2); break;
+    case 4: LAUNCH(4); break;
+    default: LAUNCH(8); break;
+  }
+#undef LAUNCH
+  return check_launch("interval_move_kernel");
+}
+
 }  // namespace
 }  // namespace b200rl
 
@@ -437,6 +531,109 @@ int b200rl_set_intervals(const void* packed, int64_t packed_numel, void* big, in
                          void* workspace, size_t workspace_bytes, int reuse_plan, void* stream) {
   return b200rl::run_copy<1>(packed, big, big_numel, packed_numel, intervals, n_intervals,
                              elem_size, workspace, workspace_bytes, reuse_plan, stream);
+}
+
+size_t b200rl_move_workspace_bytes(int64_t n_src, int64_t n_dst, int64_t total_numel, int elem_size) {
+  if (n_src < 0 || n_dst < 0 || total_numel < 0 || elem_size <= 0) return 0;
+  return b200rl::plan_layout(nullptr, n_src, total_numel, elem_size).bytes +
+         b200rl::plan_layout(nullptr, n_dst, total_numel, elem_size).bytes;
+}
+
+int b200rl_move_intervals(const void* src, int64_t src_numel, void* dst, int64_t dst_numel,
+                          const int64_t* src_intervals, int64_t n_src, const int64_t* dst_intervals,
+                          int64_t n_dst, int64_t total_numel, int elem_size, void* workspace,
+                          size_t workspace_bytes, int reuse_plan, void* stream) {
+  return b200rl::run_move(src, src_numel, dst, dst_numel, src_intervals, n_src, dst_intervals, n_dst,
+                          total_numel, elem_size, workspace, workspace_bytes, reuse_plan, stream);
+}
+
+int b200rl_enable_peer_access(int device, int peer) {
+  using namespace b200rl;
+  if (device == peer) return B200RL_OK;
+  int can = 0;
+  B200RL_CUDA(cudaDeviceCanAccessPeer(&can, device, peer));
+  if (!can) {
+    set_last_error("device %d cannot access peer %d", device, peer);
+    return B200RL_EUNSUPPORTED;
+  }
+  int prev = 0;
+  B200RL_CUDA(cudaGetDevice(&prev));
+  B200RL_CUDA(cudaSetDevice(device));
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    (void)cudaGetLastError();
+    e = cudaSuccess;
+  }
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    set_last_error("cudaDeviceEnablePeerAccess(%d -> %d): %s", device, peer, cudaGetErrorString(e));
+    return (int)e;
+  }
+  return B200RL_OK;
+}
+
+// ---- CUDA IPC: export a buffer of this process / map a peer process's buffer ----------------
+int b200rl_ipc_export(const void* ptr, unsigned char* handle64, int64_t* offset_bytes) {
+  using namespace b200rl;
+  B200RL_REQUIRE(ptr && handle64 && offset_bytes, "null pointer");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  // base of the allocation that contains ptr (the handle always names the whole allocation)
+  typedef int (*GetRangeFn)(unsigned long long*, size_t*, unsigned long long);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  B200RL_CUDA(cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q));
+  if (!fn || q != cudaDriverEntryPointSuccess) {
+    set_last_error("cuMemGetAddressRange is not available");
+    return B200RL_EUNSUPPORTED;
+  }
+  unsigned long long base = 0;
+  size_t size = 0;
+  const int drc = ((GetRangeFn)fn)(&base, &size, (unsigned long long)(uintptr_t)ptr);
+  if (drc != 0) {
+    set_last_error("cuMemGetAddressRange failed with driver error %d", drc);
+    return B200RL_EINVAL;
+  }
+  cudaIpcMemHandle_t h;
+  B200RL_CUDA(cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base));
+  memcpy(handle64, &h, 64);
+  *offset_bytes = (int64_t)((uintptr_t)ptr - (uintptr_t)base);
+  return B200RL_OK;
+}
+
+int b200rl_ipc_open(const unsigned char* handle64, int device, void** base_out) {
+  using namespace b200rl;
+  B200RL_REQUIRE(handle64 && base_out, "null pointer");
+  int prev = 0;
+  B200RL_CUDA(cudaGetDevice(&prev));
+  B200RL_CUDA(cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_last_error("cudaIpcOpenMemHandle on device %d: %s", device, cudaGetErrorString(e));
+    return (int)e;
+  }
+  *base_out = p;
+  return B200RL_OK;
+}
+
+int b200rl_ipc_close(void* base, int device) {
+  using namespace b200rl;
+  if (!base) return B200RL_OK;
+  int prev = 0;
+  B200RL_CUDA(cudaGetDevice(&prev));
+  B200RL_CUDA(cudaSetDevice(device));
+  cudaError_t e = cudaIpcCloseMemHandle(base);
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_last_error("cudaIpcCloseMemHandle: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  return B200RL_OK;
 }
 
 }  // extern "C"

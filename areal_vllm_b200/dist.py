@@ -93,3 +93,84 @@ def global_advantage_stats(
     mom, total_w = allreduce_stats(mom, local_loss_weight.reshape(-1).to(torch.float64), group=group)
     mean, denom = ops.moments_finalize(mom, False, bool(unbiased), float(eps))
     return mean, denom, total_w
+
+
+# ------------------------------------------------------------------------------------------------
+# peer memory: let a kernel on this rank's GPU read another rank's flat parameter buffer
+# ------------------------------------------------------------------------------------------------
+class PeerBuffer:
+    """A 1-D buffer that lives in ANOTHER process's GPU memory (same node), mapped into this
+    process through CUDA IPC with this rank's GPU as the accessing device. Only what the
+    interval kernels need: ``data_ptr() / numel() / dtype / element_size()``. Close it (or drop
+    it) before the owner frees the memory."""
+
+    def __init__(self, handle: bytes, offset_bytes: int, numel: int, dtype: torch.dtype,
+                 device: torch.device):
+        import ctypes
+
+        from . import _lib
+
+        self.dtype, self._numel, self.device = dtype, int(numel), torch.device(device)
+        base = ctypes.c_void_p()
+        buf = (ctypes.c_ubyte * 64).from_buffer_copy(handle)
+        _lib.check(_lib.lib.b200rl_ipc_open(buf, self.device.index, ctypes.byref(base)), "b200rl_ipc_open")
+        self._base = base.value
+        self._ptr = self._base + int(offset_bytes)
+        self.is_peer = True
+
+    def data_ptr(self) -> int:
+        return self._ptr
+
+    def numel(self) -> int:
+        return self._numel
+
+    def element_size(self) -> int:
+        return torch.empty((), dtype=self.dtype).element_size()
+
+    def is_contiguous(self) -> bool:
+        return True
+
+    def close(self) -> None:
+        if getattr(self, "_base", None):
+            from . import _lib
+
+            _lib.lib.b200rl_ipc_close(self._base, self.device.index)
+            self._base = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def export_buffer(t: torch.Tensor) -> Tuple[bytes, int, int, torch.dtype]:
+    """Picklable description of a contiguous CUDA tensor of THIS process for ``PeerBuffer``.
+    The tensor must stay alive (and at the same address) while peers have it open. Works for
+    ordinary caching-allocator memory (cudaMalloc blocks), not for expandable segments."""
+    import ctypes
+
+    from . import _lib
+
+    if not (t.is_cuda and t.is_contiguous()):
+        raise RuntimeError("only contiguous CUDA tensors can be exported")
+    handle = (ctypes.c_ubyte * 64)()
+    off = ctypes.c_int64()
+    with torch.cuda.device(t.device):
+        _lib.check(_lib.lib.b200rl_ipc_export(ctypes.c_void_p(t.data_ptr()), handle, ctypes.byref(off)),
+                   "b200rl_ipc_export")
+    return bytes(handle), int(off.value), t.numel(), t.dtype
+
+
+def open_peer_buffer(t: Optional[torch.Tensor], src: int, group=None, device=None):
+    """Collective over ``group``: rank ``src`` (a global rank) exports ``t``; every other rank
+    returns a ``PeerBuffer`` aliasing it, readable by kernels on ``device`` (default: the current
+    CUDA device). ``src`` itself gets ``t`` back."""
+    me = dist.get_rank()
+    box = [export_buffer(t) if me == src else None]
+    dist.broadcast_object_list(box, src=src, group=group)
+    if me == src:
+        return t
+    handle, off, numel, dtype = box[0]
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    return PeerBuffer(handle, off, numel, dtype, dev)

@@ -28,6 +28,7 @@ __all__ = [
     "set_intervals_fp32",
     "set_intervals_fp16",
     "set_intervals_bf16",
+    "move_intervals",
     "clear_plan_cache",
 ]
 
@@ -178,3 +179,44 @@ slice_intervals_bf16 = _typed_slice(torch.bfloat16)
 set_intervals_fp32 = _typed_set(torch.float32)
 set_intervals_fp16 = _typed_set(torch.float16)
 set_intervals_bf16 = _typed_set(torch.bfloat16)
+
+
+def move_intervals(
+    src: torch.Tensor,
+    dst: torch.Tensor,
+    src_intervals_cuda: torch.Tensor,
+    dst_intervals_cuda: torch.Tensor,
+    total_size: Optional[int] = None,
+) -> None:
+    """``set_intervals(slice_intervals(src, src_intervals), dst, dst_intervals)`` in one kernel
+    and without the intermediate buffer (extension; the reference leaves it as a TODO at
+    real_llm_api.py:719-720). Both interval lists must describe ``total_size`` elements in the
+    same order; they may cut the stream differently. ``src`` may be a peer GPU's buffer opened
+    with ``areal_vllm_b200.dist.open_peer_buffer`` - then this replaces the reference's
+    slice -> chunked_bcast -> set sequence (real_llm_api.py:721-805) with one pass of NVLink
+    loads; ordering against the owner of ``src`` stays with the caller. In place; returns None."""
+    if src.dtype not in _SUPPORTED:
+        raise NotImplementedError(src.dtype)
+    ops._check_intervals(src_intervals_cuda)
+    ops._check_intervals(dst_intervals_cuda)
+    if total_size is None:
+        total_size = int((src_intervals_cuda[:, 1] - src_intervals_cuda[:, 0]).sum().item())
+    if total_size == 0:
+        return None
+    es = src.element_size()
+    key = ("move", src_intervals_cuda.data_ptr(), src_intervals_cuda._version, src_intervals_cuda.shape[0],
+           dst_intervals_cuda.data_ptr(), dst_intervals_cuda._version, dst_intervals_cuda.shape[0],
+           total_size, es, src.numel(), dst.numel(), dst.device.index)
+    hit = _PLAN_CACHE.get(key)
+    if hit is not None:
+        _PLAN_CACHE.move_to_end(key)
+        ws, reuse = hit[0], True
+    else:
+        nbytes = _lib.lib.b200rl_move_workspace_bytes(src_intervals_cuda.shape[0], dst_intervals_cuda.shape[0],
+                                                      total_size, es)
+        ws, reuse = _lib.workspace(nbytes, dst.device), False
+        _PLAN_CACHE[key] = (ws, (src_intervals_cuda, dst_intervals_cuda))
+        while len(_PLAN_CACHE) > _PLAN_CACHE_MAX:
+            _PLAN_CACHE.popitem(last=False)
+    ops.move_intervals_raw(src, dst, src_intervals_cuda, dst_intervals_cuda, total_size, ws, reuse)
+    return None

@@ -15,6 +15,8 @@ from __future__ import annotations
 
 from typing import List, Optional, Tuple
 
+import ctypes
+
 import torch
 
 from . import _lib
@@ -874,3 +876,32 @@ def set_intervals_op(
             ptr(workspace), workspace.numel(), int(reuse_plan), stream_handle(dev),
         )
     check(rc, "b200rl_set_intervals")
+
+
+def move_intervals_raw(src, dst: Tensor, src_intervals: Tensor, dst_intervals: Tensor,
+                       total_size: int, workspace: Tensor, reuse_plan: bool) -> None:
+    """dst[dst_intervals] <- src[src_intervals] with no packed staging buffer. ``src`` is a tensor
+    on ``dst``'s device or a ``dist.PeerBuffer`` (another rank's memory, read over NVLink);
+    everything else is on ``dst``'s device, where the kernel runs. Eager only (in-place on dst)."""
+    peer = bool(getattr(src, "is_peer", False))
+    _lib.require_cuda(dst=dst, workspace=workspace)
+    if not peer:
+        _lib.require_cuda(src=src)
+    _lib.require_contiguous(src=src, dst=dst)
+    if src.dtype != dst.dtype:
+        raise RuntimeError("Source and destination tensors must have the same dtype")
+    ns, nd = _check_intervals(src_intervals), _check_intervals(dst_intervals)
+    dev = dst.device
+    if src_intervals.device != dev or dst_intervals.device != dev or workspace.device != dev:
+        raise RuntimeError("intervals and workspace must be on the destination's device")
+    if src.device != dev:
+        if peer:
+            raise RuntimeError(f"the peer buffer was opened for {src.device}, the destination is on {dev}")
+        # a tensor of this process on another of its GPUs
+        check(lib.b200rl_enable_peer_access(dev.index, src.device.index), "b200rl_enable_peer_access")
+    with _on(dev):
+        rc = lib.b200rl_move_intervals(
+            ctypes.c_void_p(src.data_ptr()), src.numel(), ptr(dst), dst.numel(), ptr(src_intervals), ns,
+            ptr(dst_intervals), nd, int(total_size), src.element_size(), ptr(workspace),
+            workspace.numel(), int(reuse_plan), stream_handle(dev))
+    check(rc, "b200rl_move_intervals")

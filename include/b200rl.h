@@ -290,6 +290,31 @@ int b200rl_set_intervals(const void* packed, int64_t packed_numel, void* big, in
                          const int64_t* intervals, int64_t n_intervals, int elem_size,
                          void* workspace, size_t workspace_bytes, int reuse_plan, void* stream);
 
+/* Fused slice -> set without the packed staging buffer (the kernel asked for
+ * by the TODO at realhf/impl/model/nn/real_llm_api.py:719-720, and with `src` pointing at a peer
+ * GPU's flat parameter buffer the replacement of slice_intervals -> chunked_bcast ->
+ * set_intervals, real_llm_api.py:721-805). Equivalent to
+ *   set_intervals(slice_intervals(src, src_intervals), dst, dst_intervals)
+ * where both interval lists sum to total_numel elements but may cut the stream differently.
+ * Intervals, workspace and dst live on the launching device; src may be peer memory that the
+ * launching device can access (b200rl_enable_peer_access). The kernel never waits on another
+ * GPU: ordering against the owner of `src` is the caller's (events / barrier). */
+size_t b200rl_move_workspace_bytes(int64_t n_src, int64_t n_dst, int64_t total_numel, int elem_size);
+int b200rl_move_intervals(const void* src, int64_t src_numel, void* dst, int64_t dst_numel,
+                          const int64_t* src_intervals, int64_t n_src, const int64_t* dst_intervals,
+                          int64_t n_dst, int64_t total_numel, int elem_size, void* workspace,
+                          size_t workspace_bytes, int reuse_plan, void* stream);
+/* cudaDeviceEnablePeerAccess(device -> peer), idempotent; B200RL_EUNSUPPORTED when impossible. */
+int b200rl_enable_peer_access(int device, int peer);
+/* CUDA IPC plumbing for the peer-memory use of b200rl_move_intervals (no reference counterpart:
+ * the reference stages through NCCL). export: 64-byte handle of the allocation containing `ptr`
+ * and ptr's byte offset inside it. open: map that allocation with `device` (the CONSUMER's GPU)
+ * current, peer access enabled lazily; returns the mapped base. close: unmap. A handle can be
+ * opened once per process and never by the exporting process. */
+int b200rl_ipc_export(const void* ptr, unsigned char* handle64, int64_t* offset_bytes);
+int b200rl_ipc_open(const unsigned char* handle64, int device, void** base_out);
+int b200rl_ipc_close(void* base, int device);
+
 /* host: merge touching neighbours [a,b),[b,c) -> [a,c), order preserving, no sort.
  * in/out: n (resp. return value) pairs of uint64. out may alias in. */
 size_t b200rl_merge_intervals(const uint64_t* in, size_t n, uint64_t* out);
