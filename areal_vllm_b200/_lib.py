@@ -94,6 +94,11 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_int32, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "b200rl_gae_2d_olp": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
+         c_int32, c_float, c_float, c_void_p],
+    ),
     "b200rl_move_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int]),
     "b200rl_move_intervals": (
         c_int,

@@ -192,3 +192,56 @@ def get_packed_rewards(
                                  seq_no_eos_mask, float(kl_ctl), float(clip_reward_value),
                                  bool(mask_no_eos_with_zero))
     return kl, tot
+
+
+def gae_2d_olp(
+    rewards: torch.Tensor,
+    values: torch.Tensor,
+    done: torch.Tensor,
+    done_y_indices: torch.Tensor,
+    cu_num_dones: torch.Tensor,
+    max_num_dones: int,
+    is_truncate: torch.Tensor,
+    gamma: float,
+    lmbda: float,
+):
+    """Binding twin of ``cugae.gae_2d_olp`` (ref csrc/cugae/gae.cu:94-131; same argument order,
+    checks and error class). Returns ``[adv, ret]``, both ``zeros_like(rewards)``-initialised."""
+    for name, t in (("rewards", rewards), ("values", values), ("done", done),
+                    ("done_y_indices", done_y_indices), ("cu_num_dones", cu_num_dones),
+                    ("is_truncate", is_truncate)):
+        if not t.is_cuda:
+            raise RuntimeError(f"{name} must be on CUDA")
+        if not t.is_contiguous():
+            raise RuntimeError(f"{name} must be contiguous")
+    if rewards.dim() != 2:
+        raise RuntimeError("rewards must be [batch, horizon]")
+    B, H = rewards.shape
+    n_dones = done_y_indices.numel()
+    if tuple(values.shape) != (B, H + 1) or tuple(done.shape) != (B, H + 1):
+        raise RuntimeError(f"values and done must have shape ({B}, {H + 1})")
+    if tuple(cu_num_dones.shape) != (B + 1,) or tuple(is_truncate.shape) != (n_dones,):
+        raise RuntimeError("cu_num_dones must be [batch + 1] and is_truncate [num_dones]")
+    if done_y_indices.dtype != torch.int32 or cu_num_dones.dtype != torch.int32:
+        raise RuntimeError("done_y_indices and cu_num_dones must be int32")
+    if is_truncate.dtype != torch.bool or done.dtype != torch.bool:
+        raise RuntimeError("is_truncate and done must be bool")
+    if rewards.dtype != torch.float32 or values.dtype != torch.float32:
+        raise RuntimeError("rewards and values must be float32")
+    adv, ret = torch.zeros_like(rewards), torch.zeros_like(rewards)
+    dev = rewards.device
+    with torch.cuda.device(dev):
+        rc = _lib.lib.b200rl_gae_2d_olp(
+            _lib.ptr(rewards), _lib.ptr(values), _lib.ptr(done.view(torch.uint8)), _lib.ptr(done_y_indices),
+            _lib.ptr(cu_num_dones), _lib.ptr(is_truncate.view(torch.uint8)), _lib.ptr(adv), _lib.ptr(ret),
+            B, H, int(max_num_dones), float(gamma), float(lmbda), _lib.stream_handle(dev))
+    _lib.check(rc, "b200rl_gae_2d_olp")
+    return [adv, ret]
+
+
+def gae_2d_nolp(rewards, values, on_reset, on_reset_y_indices, cu_num_resets, max_num_resets,
+                bootstrap, gamma, lmbda):
+    """Binding twin of ``cugae.gae_2d_nolp``. The reference's host function launches the
+    *olp* kernel with these arguments (csrc/cugae/gae.cu:199), so that is what runs here too."""
+    return gae_2d_olp(rewards, values, on_reset, on_reset_y_indices, cu_num_resets, max_num_resets,
+                      bootstrap, gamma, lmbda)

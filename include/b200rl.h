@@ -162,6 +162,20 @@ int b200rl_gae_1d_nolp_misalign_noalloc(const float* rewards, const float* value
                                         float* adv, float* ret, int32_t batch, int64_t total,
                                         float gamma, float lam, void* stream);
 
+/* Padded [B, H] GAE with episode boundaries inside a row.
+ * ref: csrc/cugae/gae.cu:62-131 (gae_2d_olp); gae_2d_nolp (:133-206) launches the same kernel
+ * (:199), so both bindings map here. rewards [B,H], values / done [B,H+1] contiguous,
+ * done_y_indices [num_dones] int32 (time indices of the dones, row after row), cu_num_dones
+ * [B+1] int32, is_truncate [num_dones] bool. Segment s of row b covers
+ * [s ? y[cu[b]+s-1] : 0, s == last ? H : y[cu[b]+s]); the next value of a segment's final step
+ * is 0 when done[b, t+1]; a non-final segment with is_truncate gets lastgae = 0 at its final
+ * step. adv / ret must be zero-filled by the caller (as at::zeros_like, gae.cu:117-118) if the
+ * segments may leave steps uncovered. Bit-identical to the reference kernel. */
+int b200rl_gae_2d_olp(const float* rewards, const float* values, const uint8_t* done,
+                      const int32_t* done_y_indices, const int32_t* cu_num_dones,
+                      const uint8_t* is_truncate, float* adv, float* ret, int32_t batch,
+                      int32_t horizon, int32_t max_num_dones, float gamma, float lam, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * H2  clipped PPO / GRPO actor loss with decoupled-PPO behaviour weights.
  * ref: areal/utils/functional.py:124-188 (ppo_actor_loss_fn);

@@ -68,6 +68,22 @@ def gae_cuda_order(rewards, values, cu_seqlens, bootstrap, gamma: float, lam: fl
     return adv, ret
 
 
+def gae_2d_olp(rewards, values, done, done_y_indices, cu_num_dones, is_truncate, gamma: float, lam: float):
+    """csrc/cugae/gae.cu:62-92 (gae_kernel_2d_olp) on [B,H] / [B,H+1] arrays."""
+    r = np.ascontiguousarray(rewards, dtype=np.float32)
+    v = np.ascontiguousarray(values, dtype=np.float32)
+    d = np.ascontiguousarray(np.asarray(done) != 0, dtype=np.uint8)
+    y = np.ascontiguousarray(done_y_indices, dtype=np.int32)
+    cu = np.ascontiguousarray(cu_num_dones, dtype=np.int32)
+    tr = np.ascontiguousarray(np.asarray(is_truncate) != 0, dtype=np.uint8)
+    B, H = r.shape
+    assert v.shape == (B, H + 1) and d.shape == (B, H + 1) and cu.shape == (B + 1,)
+    adv, ret = np.zeros_like(r), np.zeros_like(r)
+    lib().oracle_gae_2d_olp(_p(r), _p(v), _p(d), _p(y), _p(cu), _p(tr), ctypes.c_int(B), ctypes.c_int(H),
+                            ctypes.c_float(gamma), ctypes.c_float(lam), _p(adv), _p(ret))
+    return adv, ret
+
+
 def gae_f64(rewards, values, cu_seqlens, bootstrap, gamma: float, lam: float):
     r = np.ascontiguousarray(rewards, dtype=np.float32)
     v = np.ascontiguousarray(values, dtype=np.float32)

@@ -123,3 +123,33 @@ int64_t oracle_merge_intervals(const uint64_t* in, int64_t n, uint64_t* out) {
   }
   return m;
 }
+
+
+/* Padded 2-D GAE, csrc/cugae/gae.cu:62-92 (gae_kernel_2d_olp), one (row, segment) at a time,
+ * with nvcc's FMA contraction written out. */
+void oracle_gae_2d_olp(const float* rewards, const float* values, const uint8_t* done,
+                       const int32_t* done_y, const int32_t* cu_dones, const uint8_t* is_truncate,
+                       int batch, int horizon, float gamma, float lam, float* adv, float* ret) {
+  const float c = gamma * lam;
+  for (int b = 0; b < batch; ++b) {
+    const int c0 = cu_dones[b];
+    const int breadth = cu_dones[b + 1] - c0 + 1;
+    const float* r = rewards + (long)b * horizon;
+    const float* v = values + (long)b * (horizon + 1);
+    const uint8_t* dn = done + (long)b * (horizon + 1);
+    for (int s = 0; s < breadth; ++s) {
+      const int t_start = s == 0 ? 0 : done_y[c0 + s - 1];
+      const int t_end = s == breadth - 1 ? horizon : done_y[c0 + s];
+      const int abandon = s != breadth - 1 && is_truncate[c0 + s];
+      float last = 0.0f;
+      for (int t = t_end - 1; t >= t_start; --t) {
+        const float nv = (t == t_end - 1 && dn[t + 1]) ? 0.0f : v[t + 1];
+        const float d = fmaf(gamma, nv, r[t]) - v[t];
+        last = fmaf(c, last, d);
+        if (t == t_end - 1 && abandon) last = 0.0f;
+        adv[(long)b * horizon + t] = last;
+        ret[(long)b * horizon + t] = last + v[t];
+      }
+    }
+  }
+}

@@ -185,3 +185,25 @@ def test_sft_loss_golden(k):
     np.testing.assert_allclose(stat["loss"].numpy(), g["stat_loss"], rtol=1e-6, atol=1e-7)
     assert np.array_equal(stat["vocab_min_logits"].numpy(), g["stat_vocab_min_logits"])
     assert np.array_equal(stat["vocab_max_logits"].numpy(), g["stat_vocab_max_logits"])
+
+
+def test_gae_2d_oracle_reduces_to_1d():
+    """The 2-D restatement (gae.cu:62-92) on rows without inner dones equals the pinned 1-D
+    CUDA-order oracle (gae.cu:10-28) bit for bit; with dones, segments are independent."""
+    rng = np.random.default_rng(0)
+    B, H = 5, 40
+    r = rng.standard_normal((B, H)).astype(np.float32)
+    v = rng.standard_normal((B, H + 1)).astype(np.float32)
+    done = np.zeros((B, H + 1), dtype=bool)
+    done[:, H] = [True, False, True, False, False]
+    cu0 = np.zeros(B + 1, np.int32)
+    a2, t2 = cpu_ref.gae_2d_olp(r, v, done, np.zeros(0, np.int32), cu0, np.zeros(0, bool), 0.99, 0.95)
+    cu1 = (np.arange(B + 1) * H).astype(np.int32)
+    a1, t1 = cpu_ref.gae_cuda_order(r.reshape(-1), v.reshape(-1), cu1, ~done[:, H], 0.99, 0.95)
+    assert np.array_equal(a2.reshape(-1), a1) and np.array_equal(t2.reshape(-1), t1)
+    # one inner done at t=10 in row 0, truncated: adv[9] = 0, ret[9] = v[9]; first part unaffected by the tail
+    done[0, 10] = True
+    cu = np.array([0, 1, 1, 1, 1, 1], np.int32)
+    a3, t3 = cpu_ref.gae_2d_olp(r, v, done, np.array([10], np.int32), cu, np.array([True]), 0.99, 0.95)
+    assert a3[0, 9] == 0.0 and t3[0, 9] == v[0, 9]
+    assert np.array_equal(a3[0, 10:], a2[0, 10:]) and np.array_equal(a3[1:], a2[1:])
