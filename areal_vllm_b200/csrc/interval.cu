@@ -18,8 +18,28 @@
 namespace b200rl {
 namespace {
 
-constexpr int kTileBytes = 16384;     // packed bytes per warp tile
-constexpr int kCopyWarps = 8;         // warps per CTA in the copy kernel
+#ifndef B200RL_IV_TILE
+#define B200RL_IV_TILE 16384
+#endif
+#ifndef B200RL_IV_WARPS
+#define B200RL_IV_WARPS 8
+#endif
+#ifndef B200RL_IV_OCC
+#define B200RL_IV_OCC 4
+#endif
+#ifndef B200RL_IV_U
+#define B200RL_IV_U 4
+#endif
+#ifndef B200RL_IV_US
+#define B200RL_IV_US 4
+#endif
+#ifndef B200RL_IV_TILE_MAX
+#define B200RL_IV_TILE_MAX 32768
+#endif
+constexpr int kTileBytes = B200RL_IV_TILE;   // smallest packed bytes per warp tile (workspace sizing)
+constexpr int kTileBytesMax = B200RL_IV_TILE_MAX;
+constexpr int kCopyWarps = B200RL_IV_WARPS;  // warps per CTA in the copy kernel
+constexpr int kCopyOcc = B200RL_IV_OCC;      // CTAs per SM the copy kernels are compiled for
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;         // intervals per thread in the local scan
 constexpr int kScanBlock = kScanThreads * kScanItems;  // 2048 intervals per CTA
@@ -33,12 +53,22 @@ struct PlanLayout {
   size_t bytes;
 };
 
-__host__ PlanLayout plan_layout(void* ws, int64_t n, int64_t packed_numel, int elem_size) {
+// Tile size: 16 KiB keeps small copies parallel; large copies take bigger tiles so that the
+// per-tile start-up (three dependent metadata loads) is amortised. A pure function of the packed
+// size, so a cached plan and a later call agree.
+__host__ int pick_tile_bytes(int64_t packed_bytes) {
+  int tile = kTileBytes;
+  while (tile < kTileBytesMax && packed_bytes / (2 * (int64_t)tile) >= (int64_t)kNumSMs * 64) tile *= 2;
+  return tile;
+}
+
+__host__ PlanLayout plan_layout(void* ws, int64_t n, int64_t packed_numel, int elem_size,
+                                int tile_bytes = kTileBytes) {
   PlanLayout L;
   L.nb = (n + kScanBlock - 1) / kScanBlock;
   if (L.nb < 1) L.nb = 1;
   int64_t packed_bytes = packed_numel * (int64_t)elem_size;
-  L.num_tiles = (packed_bytes + kTileBytes - 1) / kTileBytes;
+  L.num_tiles = (packed_bytes + tile_bytes - 1) / tile_bytes;
   char* p = (char*)ws;
   size_t off = 0;
   L.hdr = (int64_t*)(p + off);
@@ -151,14 +181,14 @@ interval_add_base(int64_t* __restrict__ offsets, const int64_t* __restrict__ blo
 // (upper_bound - 1, which skips empty intervals).
 __global__ void __launch_bounds__(256)
 interval_partition(const int64_t* __restrict__ offsets, int64_t n, int32_t* __restrict__ tile_first,
-                   int64_t num_tiles, int elem_shift) {
+                   int64_t num_tiles, int elem_shift, int tile_bytes) {
   int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (t > num_tiles) return;
   if (t == num_tiles) {
     tile_first[t] = (int32_t)n;
     return;
   }
-  const int64_t pos = (t * (int64_t)kTileBytes) >> elem_shift;  // first packed element of tile
+  const int64_t pos = (t * (int64_t)tile_bytes) >> elem_shift;  // first packed element of tile
   int64_t lo = 0, hi = n + 1;  // upper_bound over offsets[0..n]
   while (lo < hi) {
     int64_t mid = (lo + hi) >> 1;
@@ -214,7 +244,7 @@ __device__ __forceinline__ void copy_piece_w(const char* s, char* d, int64_t byt
     bytes -= head;
   }
   const int64_t nv = bytes / W;
-  constexpr int U = 4;
+  constexpr int U = B200RL_IV_U;
   int64_t v = lane;
   for (; v + 32 * (U - 1) < nv; v += 32 * U) {
     typename VecT<W>::type r[U];
@@ -259,7 +289,7 @@ __device__ __forceinline__ void copy_piece_shift(const char* s, char* d, int64_t
   const char* a = s - ph;                                               // 16-B aligned
   const int64_t nv = bytes >= 32 ? (bytes - 16) / 16 : 0;               // keep the over-read inside
   const unsigned k = ph >> 2, bits = (ph & 3) * 8;
-  constexpr int U = 4;
+  constexpr int U = B200RL_IV_US;
   for (int64_t v0 = 0; v0 < nv; v0 += 32 * U) {
     uint4 lo[U], ex[U];
 #pragma unroll
@@ -321,11 +351,11 @@ __device__ __forceinline__ void copy_piece(const char* s, char* d, int64_t bytes
 
 // MODE 0: slice (big -> packed).  MODE 1: set (packed -> big).
 template <int MODE, int ES>
-__global__ void __launch_bounds__(kCopyWarps * 32, 4)
+__global__ void __launch_bounds__(kCopyWarps * 32, kCopyOcc)
 interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
                      const int64_t* __restrict__ intervals, const int64_t* __restrict__ offsets,
                      const int32_t* __restrict__ tile_first, const int64_t* __restrict__ hdr,
-                     int64_t n, int64_t num_tiles) {
+                     int64_t n, int64_t num_tiles, int tile_bytes) {
   const int lane = threadIdx.x & 31;
   const int64_t tile = (int64_t)blockIdx.x * kCopyWarps + (threadIdx.x >> 5);
   if (tile >= num_tiles) return;
@@ -333,8 +363,8 @@ interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
   int64_t total_elems = hdr[0];
   if (total_elems > hdr[3]) total_elems = hdr[3];  // never write past the packed buffer
   const int64_t total_bytes = total_elems * ES;
-  int64_t p0 = tile * (int64_t)kTileBytes;
-  int64_t p1 = p0 + kTileBytes;
+  int64_t p0 = tile * (int64_t)tile_bytes;
+  int64_t p1 = p0 + tile_bytes;
   if (p1 > total_bytes) p1 = total_bytes;
   int64_t i = tile_first[tile];
   while (p0 < p1 && i < n) {
@@ -359,13 +389,13 @@ interval_copy_kernel(const char* __restrict__ src, char* __restrict__ dst,
 // intervals cut it one way, the destination intervals another; a tile walks both lists and moves
 // the intersections. `src` may be peer memory (NVLink loads): nothing here waits on another GPU.
 template <int ES>
-__global__ void __launch_bounds__(kCopyWarps * 32, 4)
+__global__ void __launch_bounds__(kCopyWarps * 32, kCopyOcc)
 interval_move_kernel(const char* __restrict__ src, char* __restrict__ dst,
                      const int64_t* __restrict__ s_iv, const int64_t* __restrict__ s_off,
                      const int32_t* __restrict__ s_first, const int64_t* __restrict__ s_hdr, int64_t s_n,
                      const int64_t* __restrict__ d_iv, const int64_t* __restrict__ d_off,
                      const int32_t* __restrict__ d_first, const int64_t* __restrict__ d_hdr, int64_t d_n,
-                     int64_t num_tiles) {
+                     int64_t num_tiles, int tile_bytes) {
   const int lane = threadIdx.x & 31;
   const int64_t tile = (int64_t)blockIdx.x * kCopyWarps + (threadIdx.x >> 5);
   if (tile >= num_tiles) return;
@@ -373,8 +403,8 @@ interval_move_kernel(const char* __restrict__ src, char* __restrict__ dst,
   int64_t total_elems = s_hdr[0] < d_hdr[0] ? s_hdr[0] : d_hdr[0];
   if (total_elems > s_hdr[3]) total_elems = s_hdr[3];
   const int64_t total_bytes = total_elems * ES;
-  int64_t p0 = tile * (int64_t)kTileBytes;
-  int64_t p1 = p0 + kTileBytes;
+  int64_t p0 = tile * (int64_t)tile_bytes;
+  int64_t p1 = p0 + tile_bytes;
   if (p1 > total_bytes) p1 = total_bytes;
   int64_t i = s_first[tile], j = d_first[tile];
   int64_t sob = 0, soe = -1, sst = 0, dob = 0, doe = -1, dst_start = 0;
@@ -413,14 +443,14 @@ int elem_shift_of(int elem_size) {
 }
 
 int build_plan(const PlanLayout& L, const int64_t* intervals, int64_t n, int64_t big_numel,
-               int64_t packed_numel, int elem_shift, cudaStream_t st) {
+               int64_t packed_numel, int elem_shift, int tile_bytes, cudaStream_t st) {
   B200RL_CUDA(cudaMemsetAsync(L.hdr, 0, 4 * sizeof(int64_t), st));
   interval_local_scan<<<(unsigned)L.nb, kScanThreads, 0, st>>>(intervals, n, big_numel, L.offsets,
                                                                L.block_sums, L.hdr);
   interval_block_scan<<<1, 1024, 0, st>>>(L.block_sums, L.nb, L.hdr, n, packed_numel);
   interval_add_base<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(L.offsets, L.block_sums, L.hdr, n);
   interval_partition<<<(unsigned)((L.num_tiles + 1 + 255) / 256), 256, 0, st>>>(
-      L.offsets, n, L.tile_first, L.num_tiles, elem_shift);
+      L.offsets, n, L.tile_first, L.num_tiles, elem_shift, tile_bytes);
   return check_launch("interval plan");
 }
 
@@ -438,14 +468,15 @@ int run_copy(const void* src, void* dst, int64_t big_numel, int64_t packed_numel
   B200RL_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "workspace must be 16-B aligned");
   B200RL_REQUIRE(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & (elem_size - 1)) == 0,
                  "src/dst must be element aligned");
-  PlanLayout L = plan_layout(ws, n, packed_numel, elem_size);
+  const int tile_bytes = pick_tile_bytes(packed_numel * (int64_t)elem_size);
+  PlanLayout L = plan_layout(ws, n, packed_numel, elem_size, tile_bytes);
   if (ws_bytes < L.bytes) {
     set_last_error("interval workspace too small: %zu < %zu", ws_bytes, L.bytes);
     return B200RL_EWORKSPACE;
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (!reuse_plan) {
-    int rc = build_plan(L, intervals, n, big_numel, packed_numel, shift, st);
+    int rc = build_plan(L, intervals, n, big_numel, packed_numel, shift, tile_bytes, st);
     if (rc) return rc;
   }
   const unsigned grid = (unsigned)((L.num_tiles + kCopyWarps - 1) / kCopyWarps);
@@ -453,7 +484,7 @@ int run_copy(const void* src, void* dst, int64_t big_numel, int64_t packed_numel
   char* d = (char*)dst;
 #define LAUNCH(ES)                                                                             \
   interval_copy_kernel<MODE, ES><<<grid, kCopyWarps * 32, 0, st>>>(s, d, intervals, L.offsets, \
-                                                                  L.tile_first, L.hdr, n, L.num_tiles)
+                                                                  L.tile_first, L.hdr, n, L.num_tiles, tile_bytes)
   switch (elem_size) {
     case 1: LAUNCH(1); break;
     case 2: LAUNCH(2); break;
@@ -479,17 +510,18 @@ int run_move(const void* src, int64_t src_numel, void* dst, int64_t dst_numel,
   B200RL_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "workspace must be 256-B aligned");
   B200RL_REQUIRE(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & (elem_size - 1)) == 0,
                  "src/dst must be element aligned");
-  PlanLayout Ls = plan_layout(ws, s_n, total_numel, elem_size);
-  PlanLayout Ld = plan_layout((char*)ws + Ls.bytes, d_n, total_numel, elem_size);
+  const int tile_bytes = pick_tile_bytes(total_numel * (int64_t)elem_size);
+  PlanLayout Ls = plan_layout(ws, s_n, total_numel, elem_size, tile_bytes);
+  PlanLayout Ld = plan_layout((char*)ws + Ls.bytes, d_n, total_numel, elem_size, tile_bytes);
   if (ws_bytes < Ls.bytes + Ld.bytes) {
     set_last_error("interval move workspace too small: %zu < %zu", ws_bytes, Ls.bytes + Ld.bytes);
     return B200RL_EWORKSPACE;
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (!reuse_plan) {
-    int rc = build_plan(Ls, s_iv, s_n, src_numel, total_numel, shift, st);
+    int rc = build_plan(Ls, s_iv, s_n, src_numel, total_numel, shift, tile_bytes, st);
     if (rc) return rc;
-    rc = build_plan(Ld, d_iv, d_n, dst_numel, total_numel, shift, st);
+    rc = build_plan(Ld, d_iv, d_n, dst_numel, total_numel, shift, tile_bytes, st);
     if (rc) return rc;
   }
   const unsigned grid = (unsigned)((Ls.num_tiles + kCopyWarps - 1) / kCopyWarps);
@@ -498,7 +530,7 @@ int run_move(const void* src, int64_t src_numel, void* dst, int64_t dst_numel,
 #define LAUNCH(ES)                                                                                \
   interval_move_kernel<ES><<<grid, kCopyWarps * 32, 0, st>>>(s, d, s_iv, Ls.offsets, Ls.tile_first, \
                                                             Ls.hdr, s_n, d_iv, Ld.offsets,        \
-                                                            Ld.tile_first, Ld.hdr, d_n, Ls.num_tiles)
+                                                            Ld.tile_first, Ld.hdr, d_n, Ls.num_tiles, tile_bytes)
   switch (elem_size) {
     case 1: LAUNCH(1); break;
     case 2: LAUNCH(2); break;

@@ -22,7 +22,11 @@ def case(name, iv):
     dst = torch.empty_like(src)
     ms2 = timeit(lambda: pkg.flatten_param.set_intervals(out, dst, intervals_cuda=ivc))
     gb = 4.0 * total / 1e9
-    print(f"{name:50s} slice {gb/ms*1e3:7.0f} GB/s  set {gb/ms2*1e3:7.0f} GB/s")
+    n_d = max(1, len(iv) // 3); per = total // n_d
+    d_iv = np.array([(i * (size // n_d), i * (size // n_d) + (per if i < n_d - 1 else total - per * (n_d - 1))) for i in range(n_d)], dtype=np.int64)
+    dvc = torch.from_numpy(d_iv).to(dev)
+    ms3 = timeit(lambda: pkg.flatten_param.move_intervals(src, dst, ivc, dvc, total))
+    print(f"{name:50s} slice {gb/ms*1e3:7.0f} GB/s  set {gb/ms2*1e3:7.0f} GB/s  move {gb/ms3*1e3:7.0f} GB/s")
     del out, dst
 n = 50000
 s = size // n
