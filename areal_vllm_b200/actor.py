@@ -358,6 +358,8 @@ def _register_stats(st, logits, c):
 
 
 def _stats_tracker():
+    if torch.compiler.is_compiling():  # the tracker is python state with locks: eager only
+        return None
     try:  # the reference's tracker, when this module is used inside AReaL
         from areal.utils import stats_tracker  # type: ignore
 

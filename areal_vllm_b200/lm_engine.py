@@ -19,6 +19,8 @@ from .functional import _as_2d
 
 
 def _stats_tracker():
+    if torch.compiler.is_compiling():  # the tracker is python state with locks: eager only
+        return None
     try:  # the reference's tracker, when this module is used inside AReaL
         from areal.utils import stats_tracker  # type: ignore
 
