@@ -234,3 +234,31 @@ def test_grpo_loss_fn_end_to_end(cuda):
     assert np.array_equal(stats["vocab_max_logits"].cpu().numpy(), logits.float().max(-1).values.numpy())
     assert np.array_equal(stats["vocab_min_logits"].cpu().numpy(), logits.float().min(-1).values.numpy())
     np.testing.assert_allclose(stats["entropy"].cpu().numpy(), ent.detach().numpy(), rtol=1e-3, atol=2e-5)
+
+
+def test_padded_rows_get_exact_zero_gradient(cuda):
+    """INTEGRATION.md 'Avoiding the padded-gradient copy': running the loss on the padded logits
+    with loss_mask = 0 on the pad rows gives the same loss, the same gradient on the real rows and
+    exact zeros on the pad rows."""
+    from areal_vllm_b200 import actor
+
+    gen = torch.Generator().manual_seed(21)
+    T, Tp, V = 300, 512, 4096
+    logits = (torch.randn(Tp, V, generator=gen) * 2).bfloat16().to(cuda)
+    mask = (torch.rand(T, generator=gen) < 0.7)
+    mask[-1] = False  # its label comes from the roll over the stream end (garbage by design)
+    data = dict(input_ids=torch.randint(0, V, (T,), generator=gen).to(cuda),
+                logprobs=(-torch.rand(T, generator=gen) * 8).to(cuda),
+                advantages=torch.randn(T, generator=gen).to(cuda), loss_mask=mask.to(cuda),
+                prox_logp=(-torch.rand(T, generator=gen) * 8).to(cuda))
+    a = logits[:T].clone().requires_grad_(True)
+    la = actor.grpo_loss_fn(a, data, 1.0, 0.2, None, None, 5.0)
+    la.backward()
+    pad = lambda t, fill=0: torch.cat([t, torch.full((Tp - T,), fill, dtype=t.dtype, device=t.device)])
+    datap = {k: pad(v) for k, v in data.items()}
+    b = logits.clone().requires_grad_(True)
+    lb = actor.grpo_loss_fn(b, datap, 1.0, 0.2, None, None, 5.0)
+    lb.backward()
+    assert torch.equal(la, lb)
+    assert torch.equal(b.grad[:T], a.grad)
+    assert int((b.grad[T:].view(torch.int16) & 0x7fff).max()) == 0  # +-0 only
