@@ -227,7 +227,7 @@ def main_reference(args):
 # ------------------------------------------------------------------------------------------
 # secondary metrics of the same path (BASELINE.json: "GAE tokens/s", interval_op GB/s)
 # ------------------------------------------------------------------------------------------
-def run_extras(dev, peak):
+def run_extras(dev, peak, compiled_baseline=False):
     import areal_vllm_b200 as pkg
     from areal_vllm_b200 import _lib
     from oracle import cpu_ref
@@ -285,6 +285,34 @@ def run_extras(dev, peak):
         out["torch_gpu_path"] = {"what": "eager torch restatement of the reference GPU path (log_softmax/gather/"
                                          "entropy in 1024-row chunks, PPO loss, min/max, backward) on this GPU",
                                  "tokens": Tt, "ms": ms, "tokens_per_s": Tt / (ms * 1e-3)}
+        if compiled_baseline:
+            # the reference decorates the per-chunk function with @torch.compile (functional.py:18-26)
+            try:
+                @torch.compile
+                def chunk_fn(xc, yc, temperature: float):
+                    la = F.log_softmax(xc.float() / temperature, dim=-1)
+                    ent = -(la.exp() * la).sum(-1)
+                    return la.gather(-1, yc.unsqueeze(-1)).squeeze(-1), ent
+
+                def compiled_step():
+                    x = lg.detach().requires_grad_(True)
+                    lps = [chunk_fn(x[lo:lo + 1024], ids[lo:lo + 1024], TEMPERATURE)[0] for lo in range(0, Tt, 1024)]
+                    lp = torch.cat(lps)
+                    n = msk.count_nonzero() or 1
+                    ratio = torch.where(msk, torch.exp(lp - prox), 0)
+                    pg = torch.max(-advt * ratio, -advt * ratio.clamp(1 - EPS_CLIP, 1 + EPS_CLIP))
+                    bw = (prox - old).exp()
+                    bm = (bw <= CAP) & msk
+                    loss = torch.where(msk, pg * torch.where(bm, bw, 0.0), 0).sum() / n
+                    _ = x.detach().min(-1).values, x.detach().max(-1).values
+                    loss.backward()
+
+                ms_c = timeit(compiled_step, iters=5, warm=3)
+                out["torch_gpu_path"]["torch_compile"] = {
+                    "what": "same, per-chunk function under torch.compile (Inductor/Triton) as in the reference",
+                    "ms": ms_c, "tokens_per_s": Tt / (ms_c * 1e-3)}
+            except Exception as e:
+                out["torch_gpu_path"]["torch_compile"] = {"error": repr(e)[:300]}
         del lg
         torch.cuda.empty_cache()
     except Exception as e:  # an OOM or similar here must not cost the headline line
@@ -647,7 +675,7 @@ def main_b200rl(args):
     if rank == 0 and world == 1 and not args.no_extras:
         del logits_bufs[:]
         torch.cuda.empty_cache()
-        extras = run_extras(dev, peak)
+        extras = run_extras(dev, peak, args.compiled_baseline)
 
     if rank == 0:
         n_mb = len(mbs)
@@ -680,6 +708,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the GAE / interval_op side metrics")
+    ap.add_argument("--compiled-baseline", action="store_true",
+                    help="extras: also time the torch.compile'd torch GPU path (adds Inductor compile time)")
     ap.add_argument("--no-fused", action="store_true", help="skip the fused-step extension measurement")
     args = ap.parse_args()
     if args.impl == "reference":
