@@ -376,6 +376,88 @@ def run_extras(dev, peak, compiled_baseline=False):
     return out
 
 # ------------------------------------------------------------------------------------------
+# BASELINE config 4 (long-CoT, strong scaling): 1,048,576 tokens of 1k-16k-token sequences, whole
+# GRPO groups sharded over the ranks by tokens, batch-level advantage normalisation (the one
+# collective of the path), 32,768-token micro-batches over a reused V=152,064 logits buffer.
+# ------------------------------------------------------------------------------------------
+def run_cfg4(dev, rank, world, steps=2):
+    import torch.distributed as dist
+
+    import areal_vllm_b200 as pkg
+    from areal_vllm_b200.actor import grpo_loss_fn
+
+    V4, MB, TOTAL, G = 152064, 32768, 1_048_576, 8
+    rng = np.random.default_rng(4)
+    lens = []
+    while sum(lens) < TOTAL:
+        lens.append(int(rng.integers(1024, 16385)))
+    lens[-1] -= sum(lens) - TOTAL
+    while len(lens) % G:
+        lens.append(0)  # pad the last group with empty sequences
+    mine = pkg.dist.shard_groups_by_tokens(lens, G, world)[rank]
+    my_lens = [lens[i] for i in mine if lens[i] > 0]
+    n_tok = sum(my_lens)
+    gen = torch.Generator(device=dev).manual_seed(40 + rank)
+    adv_raw = torch.randn(n_tok, generator=gen, device=dev)
+    mask = torch.rand(n_tok, generator=gen, device=dev) < 0.8
+    ids = torch.randint(0, V4, (n_tok,), generator=gen, device=dev)
+    lp0 = -torch.rand(n_tok, generator=gen, device=dev) * 4
+    buf = torch.empty(MB, V4, dtype=torch.bfloat16, device=dev)
+    for lo in range(0, MB, 2048):
+        buf[lo:lo + 2048] = (torch.randn(2048, V4, generator=gen, device=dev) * 2).bfloat16()
+    bounds = list(range(0, n_tok, MB)) + [n_tok]
+
+    def step():
+        # batch-level mean/std over ALL ranks + the global loss normaliser: one all-reduce
+        if world > 1:
+            mean, denom, total_w = pkg.dist.global_advantage_stats(adv_raw, mask)
+        else:
+            mom = pkg.ops.masked_moments(adv_raw, mask.float(), n_tok, None, 1)
+            mean, denom = pkg.ops.moments_finalize(mom, False, False, 1e-5)
+            total_w = mom[0, 0:1]
+        adv = ((adv_raw * mask - mean.float()) / denom.float()).float()
+        tot = torch.zeros((), device=dev)
+        for a, b in zip(bounds[:-1], bounds[1:]):
+            x = buf[: b - a].detach().requires_grad_(True)
+            data = dict(input_ids=ids[a:b], logprobs=lp0[a:b] + 0.05, advantages=adv[a:b],
+                        loss_mask=mask[a:b], prox_logp=lp0[a:b] + 0.02)
+            loss = grpo_loss_fn(x, data, 1.0, 0.2, 0.28, 3.0, 5.0)
+            # the engine's scaling: local mask count / global count (fsdp_engine.py:543-547)
+            (g,) = torch.autograd.grad(loss * (mask[a:b].sum() / total_w.float()), x)
+            tot = tot + loss.detach()
+            del g
+        return tot
+
+    step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    toks = torch.tensor([float(n_tok), ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        mx = toks.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(toks)
+        max_tok, ms, sum_tok = float(mx[0]), float(mx[1]), float(toks[0])
+    else:
+        max_tok, sum_tok = float(n_tok), float(n_tok)
+    del buf
+    torch.cuda.empty_cache()
+    return {"workload": "cfg4: 1,048,576 tokens, seqs 1k-16k, groups of 8 sharded by tokens, V=152064, "
+                        "mb 32768 tok on a reused logits buffer, batch-level AdvNorm (1 all-reduce/step), "
+                        "eps_clip 0.2/0.28, c_clip 3, cap 5",
+            "scaling": "strong", "n_gpus": world, "tokens": sum_tok, "ms_per_step_max_over_ranks": ms,
+            "tokens_per_s": sum_tok / (ms * 1e-3), "imbalance_max_over_mean_tokens": max_tok / (sum_tok / world),
+            "per_gpu_frac_of_measured_peak_at_6V_on_busiest_rank": None}
+
+
+# ------------------------------------------------------------------------------------------
 # the b200rl arm
 # ------------------------------------------------------------------------------------------
 def main_b200rl(args):
@@ -672,10 +754,22 @@ def main_b200rl(args):
             res[f"gamma={gamma},lam={lam}"] = {"tokens_all_ranks": float(tm[1]), "ms_max_over_ranks": float(tmax[0]),
                                                "tokens_per_s": float(tm[1]) / (float(tmax[0]) * 1e-3)}
         extras = {"gae_weak_scaling_65536_seqs_per_rank": res}
-    if rank == 0 and world == 1 and not args.no_extras:
+        del r_, v_, cu_, b_
+    cfg4 = None
+    if not args.no_extras:  # every rank takes part (one all-reduce per step)
         del logits_bufs[:]
         torch.cuda.empty_cache()
+        try:
+            cfg4 = run_cfg4(dev, rank, world)
+            cfg4["per_gpu_frac_of_measured_peak_at_6V_on_busiest_rank"] = (
+                cfg4["imbalance_max_over_mean_tokens"] * cfg4["tokens"] / world * 6 * 152064
+                / (cfg4["ms_per_step_max_over_ranks"] * 1e-3) / 1e9 / peak)
+        except Exception as e:  # must not cost the headline line
+            cfg4 = {"error": repr(e)[:300]}
+    if rank == 0 and world == 1 and not args.no_extras:
         extras = run_extras(dev, peak, args.compiled_baseline)
+    if extras is not None:
+        extras["cfg4_long_cot_strong_scaling"] = cfg4
 
     if rank == 0:
         n_mb = len(mbs)
