@@ -76,7 +76,7 @@ struct FusedParams {
 };
 
 __global__ void __launch_bounds__(1024)
-mask_count_kernel(const uint8_t* __restrict__ mask, int64_t T, float* __restrict__ denom) {
+mask_count_kernel(const uint8_t* __restrict__ mask, int64_t T, float* __restrict__ denom, int or_one) {
   __shared__ int red[32];
   int c = 0;
   for (int64_t i = threadIdx.x; i < T; i += 1024) c += mask[i] != 0;
@@ -87,7 +87,8 @@ mask_count_kernel(const uint8_t* __restrict__ mask, int64_t T, float* __restrict
   if (threadIdx.x == 0) {
     int t = 0;
     for (int w = 0; w < 32; w++) t += red[w];
-    denom[0] = t > 0 ? (float)t : 1.f;  // `count_nonzero() or 1` (functional.py:143)
+    // PPO: `count_nonzero() or 1` (functional.py:143). SFT: plain count, 0 gives nan (lm_engine.py:53)
+    denom[0] = (t > 0 || !or_one) ? (float)t : 1.f;
   }
 }
 
@@ -481,7 +482,7 @@ int b200rl_grpo_fused_step(const void* logits, int dtype, int64_t ld, const int6
   }
   B200RL_REQUIRE(logits && labels && prox_logp && old_logp && adv && mask && logp && lse && dlogits,
                  "null pointer");
-  mask_count_kernel<<<1, 1024, 0, st>>>(mask, T, denom);
+  mask_count_kernel<<<1, 1024, 0, st>>>(mask, T, denom, cap < -2.5f ? 0 : 1);
   FusedParams p;
   p.logits = logits; p.ld = ld; p.labels = labels; p.T = (int)T; p.V = (int)V;
   p.scale = (float)(1.4426950408889634 / (double)temperature);

@@ -25,14 +25,28 @@ struct PpoToken {
   bool clip, dual, bmask;
 };
 
-// c_clip <= 0: no dual clip. cap < 0: no cap; cap < -1.5: no behaviour weighting at all.
+// c_clip <= 0: no dual clip. cap < 0: no cap; cap < -1.5: no behaviour weighting at all;
+// cap < -2.5: not PPO at all but the SFT negative log-likelihood.
 __device__ __forceinline__ PpoToken ppo_token(float lp, float px, float ol, float A, bool m,
                                               float clip_lo, float clip_hi, float c_clip,
                                               float cap) {
+  PpoToken o;
+  if (cap < -2.5f) {
+    // negative log-likelihood (packed SFT loss, areal/engine/sft/lm_engine.py:51-53):
+    // per-token loss -logp on the masked tokens; prox / old / advantages are ignored
+    o.pgw = m ? -lp : 0.f;
+    o.ratio = 0.f;
+    o.kl = 0.f;
+    o.w = 0.f;
+    o.bkl = 0.f;
+    o.dlogp = m ? -1.f : 0.f;
+    o.clip = o.dual = false;
+    o.bmask = m;
+    return o;
+  }
   const bool has_c = c_clip > 0.f;
   const bool has_cap = cap >= 0.f;
   const bool no_bw = cap < -1.5f;
-  PpoToken o;
   // functional.py:144
   const float d = lp - px;
   const float r = m ? expf(d) : 0.f;

@@ -103,6 +103,10 @@ int b200rl_logprob_shard_combine(const float* partials, int32_t n_shards, int64_
  * to stay correct for any incoming gradient.
  */
 size_t b200rl_grpo_fused_workspace_bytes(int64_t T);
+/* b200rl_grpo_fused_step with cap == -3 is the packed SFT step (ref areal/engine/sft/lm_engine.py:
+ * 45-61 + backward): per-token loss -logp on the masked tokens, loss = sum / count(mask) with no
+ * `or 1`, dlogits = upstream * (softmax - onehot) * mask / count; prox_logp / old_logp / adv must
+ * still be valid pointers (their content is ignored), the PPO stat pointers may be NULL. */
 int b200rl_grpo_fused_step(const void* logits, int dtype, int64_t ld, const int64_t* labels,
                            int64_t T, int64_t V, float temperature, const float* prox_logp,
                            const float* old_logp, const float* adv, const uint8_t* mask,

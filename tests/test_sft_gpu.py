@@ -92,3 +92,57 @@ def test_sft_loss_all_masked_and_errors(cuda):
     out = ops.sft_loss_fwd_op(lp2, m, inp["cu_seqlens"])
     out[0].backward()
     np.testing.assert_allclose(lp2.grad.cpu().numpy(), np.full(10, -0.1, np.float32), rtol=1e-6)
+
+
+@pytest.mark.parametrize("k", range(2))
+def test_sft_fused_golden(k, cuda):
+    """the one-pass SFT step against the fixture of the real compute_packed_sft_loss + backward"""
+    from areal_vllm_b200.lm_engine import compute_packed_sft_loss_fused
+
+    g = load_golden(f"sft_{k}")
+    logits, dref = golden_logits(g)
+    x = logits.to(cuda).requires_grad_(True)
+    stats = {}
+    inp = dict(input_ids=torch.from_numpy(g["input_ids"]).to(cuda), cu_seqlens=torch.from_numpy(g["cu"]).to(cuda),
+               loss_mask=torch.from_numpy(g["loss_mask"]).to(cuda))
+    loss = compute_packed_sft_loss_fused(x, inp, loss_scale=2.5, stats=stats)  # fixture: (loss * 2.5).backward()
+    loss.backward()
+    np.testing.assert_allclose(loss.item() / 2.5, g["loss"], rtol=1e-5)
+    tol = 2e-5 if logits.dtype == torch.float32 else 8e-3
+    np.testing.assert_allclose(x.grad.float().cpu().numpy(), dref.float().numpy(), rtol=tol, atol=1e-7)
+    np.testing.assert_allclose(stats["ppl"].cpu().numpy(), g["stat_ppl"], rtol=1e-4)
+    np.testing.assert_allclose(stats["loss"].cpu().numpy(), g["stat_loss"], rtol=1e-5, atol=1e-6)
+    assert np.array_equal(stats["vocab_min_logits"].cpu().numpy(), g["stat_vocab_min_logits"])
+    assert np.array_equal(stats["vocab_max_logits"].cpu().numpy(), g["stat_vocab_max_logits"])
+
+
+def test_sft_fused_equals_separate(cuda):
+    from areal_vllm_b200.lm_engine import compute_packed_sft_loss, compute_packed_sft_loss_fused
+
+    gen = torch.Generator().manual_seed(8)
+    T, V = 700, 8192
+    logits = (torch.randn(T, V, generator=gen) * 2).bfloat16().to(cuda)
+    inp = dict(input_ids=torch.randint(0, V, (T,), generator=gen).to(cuda),
+               cu_seqlens=torch.tensor([0, 100, 350, 700], dtype=torch.int32, device=cuda),
+               loss_mask=(torch.rand(T, generator=gen) < 0.6).int().to(cuda))
+    a = logits.clone().requires_grad_(True)
+    sa = {}
+    la = compute_packed_sft_loss(a, inp, stats=sa)
+    (la * 0.37).backward()
+    b = logits.clone().requires_grad_(True)
+    sb = {}
+    lb = compute_packed_sft_loss_fused(b, inp, loss_scale=torch.tensor(0.37, device=cuda), stats=sb)
+    lb.backward()
+    np.testing.assert_allclose(lb.item(), la.item() * 0.37, rtol=1e-5)
+    np.testing.assert_allclose(b.grad.float().cpu().numpy(), a.grad.float().cpu().numpy(), rtol=8e-3, atol=1e-9)
+    for key in ("ppl", "loss", "seqlogp", "vocab_min_logits", "vocab_max_logits"):
+        np.testing.assert_allclose(sb[key].float().cpu().numpy(), sa[key].float().cpu().numpy(), rtol=1e-5, atol=1e-6, err_msg=key)
+    # no scale given and a different upstream gradient: still right (rescaled in place)
+    c = logits.clone().requires_grad_(True)
+    lc = compute_packed_sft_loss_fused(c, inp)
+    (lc * 0.37).backward()
+    np.testing.assert_allclose(c.grad.float().cpu().numpy(), a.grad.float().cpu().numpy(), rtol=8e-3, atol=1e-9)
+    # all-false mask: nan like the reference (no `or 1`)
+    inp0 = dict(inp, loss_mask=torch.zeros(T, dtype=torch.int32, device=cuda))
+    d = logits.clone().requires_grad_(True)
+    assert torch.isnan(compute_packed_sft_loss_fused(d, inp0))
