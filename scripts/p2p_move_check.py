@@ -71,8 +71,6 @@ def main():
             buf = FP.slice_intervals(src, intervals_cuda=s_c, output_size=total)
         else:
             buf = torch.empty(total, dtype=torch.bfloat16, device=dev)
-        if rank <= 1:
-            pass
         dist.broadcast(buf, src=0)
         if rank == 1:
             FP.set_intervals(buf, dst_a, intervals_cuda=d_c)

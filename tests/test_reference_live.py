@@ -95,3 +95,58 @@ def test_intervals_and_merge_fuzz():
     if merge_ref is not None:
         pairs = [(int(min(a, b)), int(max(a, b))) for a, b in rng.integers(0, 30, size=(200, 2))]
         assert cpu_ref.merge_intervals(pairs) == merge_ref(pairs)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_critic_rewards_fuzz(seed):
+    P = R.realhf_ppo_functional()
+    gen = torch.Generator().manual_seed(700 + seed)
+    T = 200 + 13 * seed
+    kind = ["mse", "huber", "huber", "mse"][seed]
+    spread = 12.0 if kind == "huber" else 1.0
+    old = torch.randn(T, generator=gen) * spread
+    val = old + 0.5 * torch.randn(T, generator=gen)
+    tgt = old + torch.randn(T, generator=gen) * spread
+    mask = (torch.rand(T, generator=gen) < 0.5) if seed % 2 == 0 else None
+    a, b = val.clone().requires_grad_(True), val.clone().requires_grad_(True)
+    l_r, s_r = P.critic_loss_fn(a, old, tgt, 0.3, loss_mask=mask, loss_fn_type=kind)
+    l_o, s_o = torch_ref.critic_loss(b, old, tgt, 0.3, mask, kind)
+    l_r.backward()
+    l_o.backward()
+    assert torch.equal(l_r, l_o) and torch.equal(a.grad, b.grad)
+    assert torch.equal(s_r["loss"], s_o["loss"]) and torch.equal(s_r["clip_mask"], s_o["clip_mask"])
+    B = 9 + seed
+    lens = torch.randint(1, 30, (B,), generator=gen)
+    cu = torch.nn.functional.pad(lens.cumsum(0), (1, 0)).int()
+    n = int(cu[-1])
+    lp = -torch.rand(n, generator=gen)
+    rf = lp + 0.1 * torch.randn(n, generator=gen)
+    sc = torch.randn(B, generator=gen) * 4
+    ne = torch.rand(B, generator=gen) < 0.4
+    for mz in (False, True):
+        k_r, t_r = P.get_packed_rewards(0.1, 2.0, lp, rf, sc, cu, ne, mask_no_eos_with_zero=mz)
+        k_o, t_o = torch_ref.packed_rewards(0.1, 2.0, lp, rf, sc, cu, ne, mz)
+        assert torch.equal(k_r, k_o) and torch.equal(t_r, t_o)
+
+
+@pytest.mark.parametrize("seed", range(2))
+def test_sft_loss_fuzz(seed):
+    fn, rec = R.sft_loss_fn()
+    gen = torch.Generator().manual_seed(800 + seed)
+    B, V = 4 + seed, 500 + 11 * seed
+    lens = torch.randint(3, 25, (B,), generator=gen)
+    cu = torch.nn.functional.pad(lens.cumsum(0), (1, 0)).int()
+    T = int(cu[-1])
+    x = (torch.randn(T, V, generator=gen) * 2).bfloat16()
+    ids = torch.randint(0, V, (T,), generator=gen)
+    mask = (torch.rand(T, generator=gen) < 0.7).int()
+    mask[1] = 1
+    a, b = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    l_r = fn(a, dict(input_ids=ids, cu_seqlens=cu, loss_mask=mask))
+    l_o, s_o = torch_ref.packed_sft_loss(b, ids, cu, mask)
+    l_r.backward()
+    l_o.backward()
+    assert torch.equal(l_r, l_o) and torch.equal(a.grad, b.grad)
+    np.testing.assert_array_equal(rec.stats["ppl"][0].numpy(), s_o["ppl"].numpy())
+    assert torch.equal(rec.stats["loss"][0], s_o["loss"])
+    assert torch.equal(rec.stats["vocab_min_logits"][0], s_o["vocab_min_logits"])
