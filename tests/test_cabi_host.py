@@ -52,6 +52,22 @@ def test_argument_errors_without_a_device():
     assert L.b200rl_interval_workspace_bytes(100000, 1 << 30, 2) > 100000 * 8
     assert L.b200rl_gae_workspace_bytes(4, 1 << 20) >= (1 << 20) // 1024 * 8
     assert L.b200rl_ppo_loss_workspace_bytes(10) >= 256 + 16
+    # entry points added after the first milestone: same convention (code + message, no device touched)
+    assert L.b200rl_critic_loss_fwd(None, None, None, None, 5, 0.2, 7, 10.0, None, None, None, None, None, None, 0, None) == -1
+    assert L.b200rl_critic_loss_workspace_bytes(1 << 20) >= 256 + 16
+    assert L.b200rl_packed_rewards(None, None, None, None, None, 2, 5, 0.1, 1.0, 0, None, None, None) == -1
+    assert L.b200rl_packed_rewards(None, None, None, None, None, 2, 0, 0.1, 1.0, 0, None, None, None) == 0  # T=0
+    assert L.b200rl_sft_loss_fwd(None, None, None, 0, 5, 2, None, None, None, None, None, None, None, 0, None) == -1
+    assert L.b200rl_sft_loss_workspace_bytes(1 << 20, 100) >= 256 + 16
+    assert L.b200rl_logprob_shard_fwd(None, 0, 8, None, 4, 8, 1.0, 1, 1, None, None) == -1
+    assert "partial" in _lib.last_error()
+    assert L.b200rl_logprob_shard_combine(None, 0, 4, 1.0, None, None, None, None, None, None) == -1
+    assert L.b200rl_move_intervals(None, 10, None, 10, None, 1, None, 1, 5, 3, None, 0, 0, None) == -1  # elem_size 3
+    assert L.b200rl_move_intervals(None, 10, None, 10, None, 0, None, 0, 0, 2, None, 0, 0, None) == 0   # nothing to move
+    assert L.b200rl_move_workspace_bytes(1000, 10, 1 << 20, 2) > 1010 * 8
+    assert L.b200rl_gae_2d_olp(None, None, None, None, None, None, None, None, 4, 10, 0, 1.0, 1.0, None) == -1
+    assert L.b200rl_gae_2d_olp(None, None, None, None, None, None, None, None, 0, 10, 0, 1.0, 1.0, None) == 0
+    assert L.b200rl_ipc_export(None, None, None) == -1
 
 
 def test_merge_intervals_host():
