@@ -421,7 +421,7 @@ def run_cfg4(dev, rank, world, steps=2):
             x = buf[: b - a].detach().requires_grad_(True)
             data = dict(input_ids=ids[a:b], logprobs=lp0[a:b] + 0.05, advantages=adv[a:b],
                         loss_mask=mask[a:b], prox_logp=lp0[a:b] + 0.02)
-            loss = grpo_loss_fn(x, data, 1.0, 0.2, 0.28, 3.0, 5.0)
+            loss = grpo_loss_fn(x, data, 1.0, 0.2, 0.28, 3.0, 5.0, stats={})
             # the engine's scaling: local mask count / global count (fsdp_engine.py:543-547)
             (g,) = torch.autograd.grad(loss * (mask[a:b].sum() / total_w.float()), x)
             tot = tot + loss.detach()
@@ -525,7 +525,8 @@ def main_b200rl(args):
         for k, mb in enumerate(dev_mbs):
             T = mb["input_ids"].numel()
             x = logits_bufs[(k + step_idx) % N_LOGITS_BUFFERS][:T].detach().requires_grad_(True)
-            loss = grpo_loss_fn_fused(x, mb, TEMPERATURE, EPS_CLIP, None, None, CAP, loss_scale=unit_scale)
+            loss = grpo_loss_fn_fused(x, mb, TEMPERATURE, EPS_CLIP, None, None, CAP, loss_scale=unit_scale,
+                                      stats={})  # the logged tensors are produced, as in the engine
             (dlogits,) = torch.autograd.grad(loss, x)
             total = total + loss.detach()
             del dlogits
@@ -545,7 +546,9 @@ def main_b200rl(args):
             if record:
                 e0, e1, e3 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
                 e0.record()
-            loss = grpo_loss_fn(x, mb, TEMPERATURE, EPS_CLIP, None, None, CAP)
+            # stats={}: every tensor the reference registers with stats_tracker (actor.py:325-365) is
+            # produced inside the timed region, as it is in the engine
+            loss = grpo_loss_fn(x, mb, TEMPERATURE, EPS_CLIP, None, None, CAP, stats={})
             if record:
                 e1.record()
             (dlogits,) = torch.autograd.grad(loss, x)
@@ -688,7 +691,7 @@ def main_b200rl(args):
                 main.wait_event(ev)
                 T = mbd["input_ids"].numel()
                 x = stage[k % 2][:T].detach().requires_grad_(True)
-                loss = grpo_loss_fn(x, mbd, TEMPERATURE, EPS_CLIP, None, None, CAP)
+                loss = grpo_loss_fn(x, mbd, TEMPERATURE, EPS_CLIP, None, None, CAP, stats={})
                 (dlogits,) = torch.autograd.grad(loss, x)
                 total = total + loss.detach()
                 fe = torch.cuda.Event()
