@@ -225,3 +225,29 @@ def test_serial_auto_dispatch_large_batch(cuda):
     a, t = PF.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 1.0, mode="serial")
     a2, t2 = PF.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 1.0, mode="serial_warp")
     assert torch.equal(a, a2) and torch.equal(t, t2)
+
+
+@pytest.mark.parametrize("gl", [(0.99, 0.95), (1.0, 1.0)])
+def test_cfg4_full(gl, cuda):
+    """BASELINE config 4's GAE shape at full size: 1,048,576 tokens in sequences of 1,024-16,384
+    tokens (seed 4). AUTO against the C port of pygae (1e-5), SERIAL bit-identical to the
+    reference kernel's order."""
+    from oracle import cpu_ref
+
+    rng = np.random.default_rng(4)
+    lens = []
+    while sum(lens) < 1_048_576:
+        lens.append(int(rng.integers(1024, 16385)))
+    lens[-1] -= sum(lens) - 1_048_576
+    B, total = len(lens), 1_048_576
+    r = rng.standard_normal(total).astype(np.float32)
+    v = rng.standard_normal(total + B).astype(np.float32)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    b = (rng.random(B) < 0.5).astype(np.float32)
+    a_ref, r_ref = cpu_ref.gae_py(r, v, cu, b, *gl)
+    adv, ret = _run((r, v, cu, b, *gl), cuda, "auto")
+    np.testing.assert_allclose(adv, a_ref, rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(ret, r_ref, rtol=1e-5, atol=1e-5)
+    a_cuda, r_cuda = cpu_ref.gae_cuda_order(r, v, cu, b, *gl)
+    adv, ret = _run((r, v, cu, b, *gl), cuda, "serial")
+    assert np.array_equal(adv, a_cuda) and np.array_equal(ret, r_cuda)
