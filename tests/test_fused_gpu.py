@@ -104,3 +104,61 @@ def test_fused_fallbacks_and_dtypes(cuda):
     with torch.no_grad():
         l = grpo_loss_fn_fused(logits.to(cuda), {k: v.to(cuda) for k, v in data.items()}, 1.0, 0.2, None, None, None)
     assert l.dim() == 0
+
+
+def test_fused_full_size_cfg2_microbatch(cuda):
+    """One full GRPO micro-batch of BASELINE config 2: 10,240 tokens x V=151,936 bf16 (3.1 GB).
+    The one-pass kernel against the separate drop-in path on the whole tensor (loss, every stat,
+    dlogits within one ulp of bf16), and a row subset of dlogits against the oracle's autograd."""
+    from areal_vllm_b200 import actor
+    from oracle import torch_ref
+
+    T, V = 10240, 151936
+    free, _ = torch.cuda.mem_get_info()
+    if free < 16 * 2**30:
+        pytest.skip("needs ~13 GB of free HBM")
+    gen = torch.Generator(device=cuda).manual_seed(2)
+    x = torch.empty(T, V, dtype=torch.bfloat16, device=cuda)
+    for lo in range(0, T, 2048):
+        x[lo:lo + 2048] = (torch.randn(2048, V, generator=gen, device=cuda) * 2).bfloat16()
+    ids = torch.randint(0, V, (T,), generator=gen, device=cuda)
+    labels = torch.roll(ids, -1)
+    rows = torch.arange(0, T, 2, device=cuda)
+    x[rows, labels[rows]] += 6.0
+    lp0 = torch_ref.logprobs_entropy(x[:64], labels[:64], 1.0)[0].mean().item()
+    data = dict(input_ids=ids, logprobs=torch.full((T,), lp0, device=cuda) + 0.05 * torch.randn(T, generator=gen, device=cuda),
+                advantages=torch.randn(T, generator=gen, device=cuda),
+                loss_mask=torch.rand(T, generator=gen, device=cuda) < 0.8,
+                prox_logp=torch.full((T,), lp0, device=cuda) + 0.02 * torch.randn(T, generator=gen, device=cuda))
+    a = x.detach().requires_grad_(True)
+    sa = {}
+    la = actor.grpo_loss_fn(a, data, 1.0, 0.4, None, None, 5.0, stats=sa)
+    (ga,) = torch.autograd.grad(la, a)
+    b = x.detach().requires_grad_(True)
+    sb = {}
+    lb = actor.grpo_loss_fn_fused(b, data, 1.0, 0.4, None, None, 5.0, stats=sb)
+    (gb,) = torch.autograd.grad(lb, b)
+    np.testing.assert_allclose(lb.item(), la.item(), rtol=1e-5)
+    for k in sa:
+        if sa[k].dtype == torch.bool:
+            assert torch.equal(sa[k], sb[k]), k
+        else:
+            assert torch.allclose(sa[k].float(), sb[k].float(), rtol=1e-5, atol=1e-6), k
+    diff = (ga.float() - gb.float()).abs()
+    tol = 8e-3 * ga.float().abs() + 1e-9
+    assert bool((diff <= tol).all())
+    del diff, tol
+    # rows of the gradient sum to ~0 (softmax minus one-hot) and a subset matches the oracle
+    pick = torch.randperm(T, generator=gen, device=cuda)[:64].sort().values
+    xs = x.detach()[pick].clone().requires_grad_(True)
+    lp_r, _ = torch_ref.logprobs_entropy(xs, labels[pick], 1.0)
+    # d loss / d logp for the picked rows from the separate path's autograd
+    full_lp = sa["new_logp"].clone()
+    from areal_vllm_b200 import functional as BF
+    lp_all = full_lp.clone().requires_grad_(True)
+    loss_all, _ = BF.ppo_actor_loss_fn(lp_all, data["prox_logp"], data["logprobs"], data["advantages"], 0.4,
+                                       data["loss_mask"], behav_imp_weight_cap=5.0)
+    (g_lp,) = torch.autograd.grad(loss_all, lp_all)
+    assert float(gb[pick].float().sum(-1).abs().max()) < 2e-2 * float(g_lp.abs().max())  # bf16 rounding only
+    (lp_r * g_lp[pick]).sum().backward()
+    np.testing.assert_allclose(gb[pick].float().cpu().numpy(), xs.grad.float().cpu().numpy(), rtol=8e-3, atol=1e-9)
