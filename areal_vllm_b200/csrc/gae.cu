@@ -97,27 +97,40 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
           d[q] = X;
         }
         if (q >= 7) {
-          float4 hi4 = *reinterpret_cast<float4*>(d + q - 3);
-          float4 lo4 = *reinterpret_cast<float4*>(d + q - 7);
-#pragma unroll 2
-          for (; q >= 7; q -= 8) {
-            float4 nhi = hi4, nlo = lo4;
-            if (q >= 15) {
-              nhi = *reinterpret_cast<float4*>(d + q - 11);
-              nlo = *reinterpret_cast<float4*>(d + q - 15);
+          // two register sets in ping-pong (no copies between them): while one set runs its 8
+          // dependent FMAs the other one's two 16-byte loads are in flight
+          auto chain8 = [&](float4& h4, float4& l4, float* at) {
+            h4.w = X = __fmaf_rn(c, X, h4.w);
+            h4.z = X = __fmaf_rn(c, X, h4.z);
+            h4.y = X = __fmaf_rn(c, X, h4.y);
+            h4.x = X = __fmaf_rn(c, X, h4.x);
+            l4.w = X = __fmaf_rn(c, X, l4.w);
+            l4.z = X = __fmaf_rn(c, X, l4.z);
+            l4.y = X = __fmaf_rn(c, X, l4.y);
+            l4.x = X = __fmaf_rn(c, X, l4.x);
+            *reinterpret_cast<float4*>(at - 3) = h4;
+            *reinterpret_cast<float4*>(at - 7) = l4;
+          };
+          float4 ah = *reinterpret_cast<float4*>(d + q - 3);
+          float4 al = *reinterpret_cast<float4*>(d + q - 7);
+          float4 bh = make_float4(0.f, 0.f, 0.f, 0.f), bl = bh;
+          while (true) {
+            const bool more1 = q >= 15;
+            if (more1) {
+              bh = *reinterpret_cast<float4*>(d + q - 11);
+              bl = *reinterpret_cast<float4*>(d + q - 15);
             }
-            hi4.w = X = __fmaf_rn(c, X, hi4.w);
-            hi4.z = X = __fmaf_rn(c, X, hi4.z);
-            hi4.y = X = __fmaf_rn(c, X, hi4.y);
-            hi4.x = X = __fmaf_rn(c, X, hi4.x);
-            lo4.w = X = __fmaf_rn(c, X, lo4.w);
-            lo4.z = X = __fmaf_rn(c, X, lo4.z);
-            lo4.y = X = __fmaf_rn(c, X, lo4.y);
-            lo4.x = X = __fmaf_rn(c, X, lo4.x);
-            *reinterpret_cast<float4*>(d + q - 3) = hi4;
-            *reinterpret_cast<float4*>(d + q - 7) = lo4;
-            hi4 = nhi;
-            lo4 = nlo;
+            chain8(ah, al, d + q);
+            q -= 8;
+            if (!more1) break;
+            const bool more2 = q >= 15;
+            if (more2) {
+              ah = *reinterpret_cast<float4*>(d + q - 11);
+              al = *reinterpret_cast<float4*>(d + q - 15);
+            }
+            chain8(bh, bl, d + q);
+            q -= 8;
+            if (!more2) break;
           }
         }
       }
