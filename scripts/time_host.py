@@ -34,3 +34,28 @@ t("grpo_loss_fn + backward", full2)
 class Cfg: mean_level, std_level, group_size = "group", "group", 8
 an = pkg.actor.AdvNorm(Cfg); a = torch.randn(64, 128, device=dev); m = torch.ones(64, 128, device=dev)
 t("AdvNorm group/group", lambda: an(a, m))
+# newer entry points
+from areal_vllm_b200 import mcore_functional as MF, ppo_functional as PF, lm_engine as LE
+def tp1():
+    xg = x.detach().requires_grad_(True)
+    l, e = MF.vocab_parallel_logprobs_entropy(xg, y, 1.0)
+    torch.autograd.grad(l.sum(), xg)
+t("vocab_parallel fwd+bwd (one shard, no group)", tp1)
+val = torch.randn(T, device=dev)
+def crit():
+    vg = val.detach().requires_grad_(True)
+    l, s = PF.critic_loss_fn(vg, val + 0.1, val - 1.0, 0.2, mask)
+    torch.autograd.grad(l, vg)
+t("critic_loss_fn + backward", crit)
+cu = torch.tensor([0, 100, 256], dtype=torch.int32, device=dev)
+sc = torch.randn(2, device=dev); ne = torch.zeros(2, dtype=torch.bool, device=dev)
+t("get_packed_rewards", lambda: PF.get_packed_rewards(0.1, 5.0, prox, old, sc, cu, ne))
+inp = dict(input_ids=y, cu_seqlens=cu, loss_mask=mask.int())
+def sft():
+    xg = x.detach().requires_grad_(True)
+    torch.autograd.grad(LE.compute_packed_sft_loss(xg, inp), xg)
+t("compute_packed_sft_loss + backward", sft)
+def sftf():
+    xg = x.detach().requires_grad_(True)
+    torch.autograd.grad(LE.compute_packed_sft_loss_fused(xg, inp), xg)
+t("compute_packed_sft_loss_fused + backward", sftf)
