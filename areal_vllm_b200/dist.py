@@ -17,7 +17,8 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_groups_by_tokens", "allreduce_stats", "global_advantage_stats"]
+__all__ = ["shard_groups_by_tokens", "shard_sequences_by_tokens", "allreduce_stats",
+           "global_advantage_stats", "sharded_group_advantage_norm"]
 
 
 def shard_groups_by_tokens(
@@ -52,6 +53,61 @@ def shard_groups_by_tokens(
             seqs.extend(range(g * group_size, (g + 1) * group_size))
         out.append(seqs)
     return out
+
+
+def shard_sequences_by_tokens(seqlens: Sequence[int], world_size: int) -> List[List[int]]:
+    """Assign single sequences to ranks so that token counts are balanced (reference analogue:
+    allocate_balanced_mbs, areal/utils/data.py:219-243, which balances by tokens at sequence
+    granularity and knows nothing about GRPO groups).
+
+    H1/H2 are per token and GAE is per sequence, so nothing on the path needs a GRPO group to sit
+    on one rank; group-level advantage statistics are additive moments and are summed over the
+    ranks by ``sharded_group_advantage_norm`` ([G, 3] fp64 in the step's one all-reduce). Whole
+    groups of long sequences balance badly (15 groups on 8 ranks: max/mean 1.11); single sequences
+    do not. Longest-processing-time greedy, then a pairwise-swap refinement; deterministic (ties
+    by index), so every rank computes the same answer locally. Zero-length sequences are kept
+    (assigned like any other) so the returned lists partition ``range(len(seqlens))``."""
+    if world_size <= 0:
+        raise ValueError("world_size must be positive")
+    lens = [int(x) for x in seqlens]
+    order = sorted(range(len(lens)), key=lambda i: (-lens[i], i))
+    load = [0] * world_size
+    assign: List[List[int]] = [[] for _ in range(world_size)]
+    for i in order:
+        r = min(range(world_size), key=lambda k: (load[k], k))
+        load[r] += lens[i]
+        assign[r].append(i)
+    # refinement: move or swap sequences between the heaviest and the lightest rank while that
+    # lowers the maximum (LPT alone leaves ~ one shortest sequence of slack)
+    for _ in range(4 * max(len(lens), 1)):
+        hi = max(range(world_size), key=lambda k: (load[k], -k))
+        lo = min(range(world_size), key=lambda k: (load[k], k))
+        gap = load[hi] - load[lo]
+        if gap <= 1:
+            break
+        best = None  # (new gap, i on hi, j on lo or None)
+        for i in assign[hi]:
+            if 0 < lens[i] < gap:
+                cand = (abs(gap - 2 * lens[i]), i, None)
+                best = cand if best is None or cand[:1] < best[:1] else best
+            for j in assign[lo]:
+                d = lens[i] - lens[j]
+                if 0 < d < gap:
+                    cand = (abs(gap - 2 * d), i, j)
+                    best = cand if best is None or cand[:1] < best[:1] else best
+        if best is None or best[0] >= gap:
+            break
+        _, i, j = best
+        assign[hi].remove(i)
+        assign[lo].append(i)
+        load[hi] -= lens[i]
+        load[lo] += lens[i]
+        if j is not None:
+            assign[lo].remove(j)
+            assign[hi].append(j)
+            load[lo] -= lens[j]
+            load[hi] += lens[j]
+    return [sorted(a) for a in assign]
 
 
 def allreduce_stats(*tensors: torch.Tensor, group=None) -> Tuple[torch.Tensor, ...]:
@@ -93,6 +149,50 @@ def global_advantage_stats(
     mom, total_w = allreduce_stats(mom, local_loss_weight.reshape(-1).to(torch.float64), group=group)
     mean, denom = ops.moments_finalize(mom, False, bool(unbiased), float(eps))
     return mean, denom, total_w
+
+
+@torch.no_grad()
+def sharded_group_advantage_norm(
+    advantages: torch.Tensor,
+    loss_mask: Optional[torch.Tensor],
+    row_group: torch.Tensor,
+    n_groups: int,
+    eps: float = 1e-5,
+    unbiased: bool = False,
+    group=None,
+    extra: Sequence[torch.Tensor] = (),
+    reduce=None,
+):
+    """AdvNorm(mean_level="group", std_level="group") when the rows of one GRPO group may live on
+    DIFFERENT ranks (sequence-granular sharding, ``shard_sequences_by_tokens``).
+
+    ``advantages`` / ``loss_mask``: this rank's padded ``[B_local, L]`` rows; ``row_group[b]`` is
+    the GLOBAL group id of row b (int64, in ``[0, n_groups)``). The masked moments
+    ``(sum m, sum x*m, sum (x*m)^2)`` of masked_normalization (ref areal/utils/functional.py:
+    100-121) are additive, so each rank reduces its rows (one launch, fp64), adds them into a
+    ``[n_groups, 3]`` table and the table is summed over the ranks in the SAME all-reduce as the
+    ``extra`` tensors (loss normaliser etc.). Returns ``(normalised [B_local, L] fp32,
+    reduced extras...)``; identical to ``AdvNorm`` on the gathered batch up to fp64 summation
+    order. ``reduce`` (testing hook) replaces the all-reduce: ``reduce(table, *extra)`` ->
+    tuple."""
+    from . import ops
+
+    x = advantages.float().contiguous()
+    B, L = x.shape
+    m = None if loss_mask is None else loss_mask.to(torch.float32).contiguous()
+    table = torch.zeros(n_groups, 3, dtype=torch.float64, device=x.device)
+    if x.numel():
+        rows = ops.masked_moments(x.view(-1), None if m is None else m.view(-1), L, None, 1)
+        table.index_add_(0, row_group.to(torch.int64), rows)
+    red = (reduce or (lambda *ts: allreduce_stats(*ts, group=group)))(table, *extra)
+    table = red[0]
+    if x.numel() == 0:
+        return (x,) + tuple(red[1:])
+    mean, denom = ops.moments_finalize(table.contiguous(), False, bool(unbiased), float(eps))
+    rg = row_group.to(torch.int64)
+    out = ops.masked_normalize(x.view(-1), None if m is None else m.view(-1), mean[rg].contiguous(), L,
+                               denom[rg].contiguous(), L, True).view(B, L)
+    return (out,) + tuple(red[1:])
 
 
 # ------------------------------------------------------------------------------------------------

@@ -52,6 +52,12 @@ def gather_partials(partial: torch.Tensor, group=None) -> torch.Tensor:
     if group is None or dist.get_world_size(group) == 1:
         return partial.unsqueeze(0)
     n = dist.get_world_size(group)
+    if partial.is_cuda and dist.get_backend(group) == "gloo":
+        # a gloo group (several ranks sharing one GPU, or a CPU-side control group): the 32-byte
+        # records travel through host memory; everything else stays on the device
+        host = torch.empty((n * partial.shape[0],) + tuple(partial.shape[1:]), dtype=partial.dtype)
+        dist.all_gather_into_tensor(host, partial.cpu().contiguous(), group=group)
+        return host.to(partial.device).view((n,) + tuple(partial.shape))
     out = torch.empty((n * partial.shape[0],) + tuple(partial.shape[1:]), dtype=partial.dtype,
                       device=partial.device)
     dist.all_gather_into_tensor(out, partial.contiguous(), group=group)

@@ -17,10 +17,11 @@ loss.backward() down to dlogits. Metric: tokens/s (whole job, all ranks).
          a copy stream) and the loss is read back to the host.
   roofline  the dominant kernel (logprob backward: 4*V bytes/token) timed with CUDA events around
          each of its launches inside the timed region, against MEASURED_PEAKS.json.
-  cpu_baseline  the CPU oracle (torch fp32 restatement of the reference) on a bounded sample.
+  cpu_baseline  the same CPU leg as --impl reference on the same bounded sample (4,096 tokens).
 
---impl reference times the reference's own CPU implementation of the path (the oracle port; the
-reference tree itself does not exist on the GPU box) with all host threads.
+--impl reference times the reference's own CPU implementation of the path with all host threads:
+the reference's own functions when a reference tree is on the box (/root/reference, or the
+pip-installed copy under baseline/_ref that travels with the snapshot), else the oracle port.
 """
 
 from __future__ import annotations
@@ -160,63 +161,106 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------
-# the reference arm / CPU baseline: the oracle port on the host cores
+# the reference arm / CPU baseline: the reference's own functions on the host cores
 # ------------------------------------------------------------------------------------------
-def cpu_step(sample_tokens: int, seed: int = 0):
-    """One pass of the hot path over a `sample_tokens`-token sample of cfg2 with the CPU oracle
-    (fp32 torch restatement of areal/utils/functional.py, eager, all host threads)."""
-    from oracle import torch_ref
-
-    gen = torch.Generator().manual_seed(seed)
-    T = sample_tokens
-    logits = (torch.randn(T, V, generator=gen) * 2).bfloat16().requires_grad_(True)
-    ids = torch.randint(0, V, (T,), generator=gen)
-    mask = torch.rand(T, generator=gen) < 0.7
-    lp0 = -torch.rand(T, generator=gen) * 4
-    old, prox = lp0 + 0.05 * torch.randn(T, generator=gen), lp0 + 0.02 * torch.randn(T, generator=gen)
-    adv_rows = torch.randn(((T + 63) // 64 + 7) // 8 * 8, 64, generator=gen)
-    t0 = time.perf_counter()
-    adv = torch_ref.adv_norm(adv_rows, torch.ones_like(adv_rows), "group", "group", GROUP).reshape(-1)[:T]
-    lp, ent = torch_ref.logprobs_entropy(logits, torch.roll(ids, -1), TEMPERATURE)
-    loss, _ = torch_ref.ppo_actor_loss(lp, prox, old, adv, EPS_CLIP, mask, None, None, CAP)
-    _ = logits.detach().min(-1).values.float(), logits.detach().max(-1).values.float()  # actor.py:351-352
-    loss.backward()
-    return time.perf_counter() - t0
+CPU_SAMPLE_TOKENS = 4096  # BASELINE.md §4 / SURVEY §8d: eager fp32 fwd+bwd keeps ~2.7 MB per token alive
 
 
-def run_cpu_baseline(budget_s: float = 20.0, sample_tokens: int = 1024):
-    torch.set_num_threads(os.cpu_count() or 1)
-    cpu_step(256)  # warm-up (thread pool, allocator)
+class CpuArm:
+    """One pass of the hot path over a bounded sample of cfg2 on the host cores, eager fp32 torch
+    with all threads. kind "reference": the reference's OWN functions (areal/utils/functional.py:
+    10-188 gather_logprobs_entropy + ppo_actor_loss_fn, AdvNorm of areal/engine/ppo/actor.py:370-604)
+    loaded from /root/reference or baseline/_ref by oracle/ref_loader.py (the @torch.compile
+    decorators are bypassed via _torchdynamo_orig_callable: Inductor's CPU backend does not build
+    here, and eager IS the reference's fp32 torch path). kind "port": oracle/torch_ref.py, the
+    line-by-line restatement pinned by tests/golden, when no reference tree is on the box."""
+
+    def __init__(self, sample_tokens: int = CPU_SAMPLE_TOKENS):
+        from oracle import ref_loader, torch_ref
+
+        torch.set_num_threads(os.cpu_count() or 1)
+        self.T = sample_tokens
+        self.kind, self.F, self.adv_norm = "port", None, None
+        if ref_loader.available():
+            try:
+                self.F = ref_loader.areal_functional()
+
+                class Cfg:
+                    mean_level, std_level, group_size = "group", "group", GROUP
+
+                self.adv_norm = ref_loader.adv_norm_class()(Cfg)
+                self.kind = "reference"
+                self.where = ref_loader.REF_ROOT
+            except Exception as e:  # a broken tree must not cost the line
+                self.F, self.why_port = None, repr(e)[:200]
+        self.torch_ref = torch_ref
+        gen = torch.Generator().manual_seed(0)
+        T = self.T
+        self.logits = (torch.randn(T, V, generator=gen) * 2).bfloat16()
+        self.ids = torch.randint(0, V, (T,), generator=gen)
+        self.mask = torch.rand(T, generator=gen) < 0.7
+        lp0 = -torch.rand(T, generator=gen) * 4
+        self.old = lp0 + 0.05 * torch.randn(T, generator=gen)
+        self.prox = lp0 + 0.02 * torch.randn(T, generator=gen)
+        self.adv_rows = torch.randn(((T + 63) // 64 + 7) // 8 * 8, 64, generator=gen)
+
+    def step(self, tokens: int | None = None) -> float:
+        T = tokens or self.T
+        logits = self.logits[:T].detach().requires_grad_(True)
+        ids, mask, old, prox = self.ids[:T], self.mask[:T], self.old[:T], self.prox[:T]
+        ones = torch.ones_like(self.adv_rows)
+        t0 = time.perf_counter()
+        if self.F is not None:
+            adv = self.adv_norm(self.adv_rows, ones).reshape(-1)[:T]
+            lp, ent = self.F.gather_logprobs_entropy(logits, torch.roll(ids, -1), TEMPERATURE)
+            loss, _ = self.F.ppo_actor_loss_fn(logprobs=lp, old_logprobs=old, advantages=adv, eps_clip=EPS_CLIP,
+                                               loss_mask=mask, c_clip=None, proximal_logprobs=prox,
+                                               behav_imp_weight_cap=CAP)
+        else:
+            adv = self.torch_ref.adv_norm(self.adv_rows, ones, "group", "group", GROUP).reshape(-1)[:T]
+            lp, ent = self.torch_ref.logprobs_entropy(logits, torch.roll(ids, -1), TEMPERATURE)
+            loss, _ = self.torch_ref.ppo_actor_loss(lp, prox, old, adv, EPS_CLIP, mask, None, None, CAP)
+        _ = logits.detach().min(-1).values.float(), logits.detach().max(-1).values.float()  # actor.py:351-352
+        loss.backward()
+        return time.perf_counter() - t0
+
+    def describe(self, n_runs: str) -> str:
+        what = (f"the reference's own areal/utils/functional.py + AdvNorm from {self.where}" if self.kind == "reference"
+                else "oracle/torch_ref.py port (no reference tree on this box)")
+        return (f"{self.T}-token sample of cfg2 (V={V}), eager fp32 torch fwd+bwd on {os.cpu_count()} host "
+                f"threads, {what}, {n_runs}")
+
+
+def run_cpu_baseline(budget_s: float = 20.0):
+    arm = CpuArm()
+    arm.step(256)  # warm-up (thread pool, allocator)
     times = []
     t_start = time.perf_counter()
     while not times or (time.perf_counter() - t_start < budget_s and len(times) < 8):
-        times.append(cpu_step(sample_tokens, seed=len(times)))
-    best = min(times)
-    return {"value": sample_tokens / best, "unit": "tokens/s", "cores": os.cpu_count() or 1, "kind": "port",
-            "sample": f"{sample_tokens}-token sample of cfg2 (V={V}), eager fp32 torch oracle fwd+bwd, "
-                      f"best of {len(times)}"}
+        times.append(arm.step())
+    return {"value": arm.T / min(times), "unit": "tokens/s", "cores": os.cpu_count() or 1, "kind": arm.kind,
+            "sample": arm.describe(f"best of {len(times)}")}
 
 
 def main_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = 1024
-    torch.set_num_threads(os.cpu_count() or 1)
+    arm = CpuArm()
     for _ in range(max(args.warmup, 1)):
-        cpu_step(256)
+        arm.step(256)
     dt = 0.0
     for k in range(args.steps):
-        dt += cpu_step(sample, seed=k)  # compute time only; input generation is outside
-    val = sample * args.steps / dt
+        dt += arm.step()  # compute time only; the (fixed) sample is generated once, outside
+    val = arm.T * args.steps / dt
     out = {
         "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "reference",
-        "config": {"workload": WORKLOAD, "note": "CPU oracle port of the reference path; each step = "
-                   f"a {sample}-token sample of the workload"},
-        "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": os.cpu_count() or 1, "kind": "port",
-                         "sample": f"{sample}-token sample per step"},
+        "config": {"workload": WORKLOAD, "note": "CPU path of the reference; each step = a "
+                   f"{arm.T}-token sample of the workload (warm-up steps use 256 tokens)"},
+        "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": os.cpu_count() or 1, "kind": arm.kind,
+                         "sample": arm.describe(f"{args.steps} timed steps")},
         "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -380,48 +424,78 @@ def run_extras(dev, peak, compiled_baseline=False):
 # GRPO groups sharded over the ranks by tokens, batch-level advantage normalisation (the one
 # collective of the path), 32,768-token micro-batches over a reused V=152,064 logits buffer.
 # ------------------------------------------------------------------------------------------
-def run_cfg4(dev, rank, world, steps=2):
+def _gather_var(x: torch.Tensor, world: int):
+    """all-gather of per-rank 1-D tensors of different lengths -> list of tensors (every rank)."""
+    import torch.distributed as dist
+
+    n = torch.tensor([x.numel()], device=x.device, dtype=torch.int64)
+    ns = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(ns, n)
+    ns = [int(v) for v in ns]
+    pad = torch.zeros(max(ns), dtype=x.dtype, device=x.device)
+    pad[: x.numel()] = x
+    out = torch.empty(world * max(ns), dtype=x.dtype, device=x.device)
+    dist.all_gather_into_tensor(out, pad)
+    return [out[r * max(ns): r * max(ns) + ns[r]] for r in range(world)]
+
+
+def run_cfg4(dev, rank, world, steps=2, check=True):
+    """-> (timing record, parity record or None). The parity record is what a data-parallel run
+    has to get right (ref fsdp_engine.py:486-491, 543-547; functional.py:108-115): the all-reduced
+    batch moments, the normalised advantages, the summed loss and d loss/d logp of the SHARDED
+    step against rank 0 recomputing all of it from the gathered per-token inputs in one piece."""
     import torch.distributed as dist
 
     import areal_vllm_b200 as pkg
+    from areal_vllm_b200 import functional as Fn
     from areal_vllm_b200.actor import grpo_loss_fn
 
-    V4, MB, TOTAL, G = 152064, 32768, 1_048_576, 8
+    V4, MB, TOTAL = 152064, 32768, 1_048_576
+    CLIP = (0.2, 0.28, 3.0, 5.0)
     rng = np.random.default_rng(4)
     lens = []
     while sum(lens) < TOTAL:
         lens.append(int(rng.integers(1024, 16385)))
     lens[-1] -= sum(lens) - TOTAL
-    while len(lens) % G:
-        lens.append(0)  # pad the last group with empty sequences
-    mine = pkg.dist.shard_groups_by_tokens(lens, G, world)[rank]
-    my_lens = [lens[i] for i in mine if lens[i] > 0]
-    n_tok = sum(my_lens)
+    # token-balanced split at SEQUENCE granularity (areal/utils/data.py:219-243); nothing in the
+    # step needs a GRPO group on one rank (batch-level statistics here; group-level ones are
+    # additive moments, see dist.sharded_group_advantage_norm)
+    mine = pkg.dist.shard_sequences_by_tokens(lens, world)[rank]
+    n_tok = sum(lens[i] for i in mine)
     gen = torch.Generator(device=dev).manual_seed(40 + rank)
     adv_raw = torch.randn(n_tok, generator=gen, device=dev)
     mask = torch.rand(n_tok, generator=gen, device=dev) < 0.8
     ids = torch.randint(0, V4, (n_tok,), generator=gen, device=dev)
     lp0 = -torch.rand(n_tok, generator=gen, device=dev) * 4
-    buf = torch.empty(MB, V4, dtype=torch.bfloat16, device=dev)
-    for lo in range(0, MB, 2048):
-        buf[lo:lo + 2048] = (torch.randn(2048, V4, generator=gen, device=dev) * 2).bfloat16()
-    bounds = list(range(0, n_tok, MB)) + [n_tok]
 
-    def step():
+    def make_buf(r):
+        g = torch.Generator(device=dev).manual_seed(400 + r)
+        b = torch.empty(MB, V4, dtype=torch.bfloat16, device=dev)
+        for lo in range(0, MB, 2048):
+            b[lo:lo + 2048] = (torch.randn(2048, V4, generator=g, device=dev) * 2).bfloat16()
+        return b
+
+    buf = make_buf(rank)
+    bounds = list(range(0, n_tok, MB)) + [n_tok]
+    old_lp, prox_lp = lp0 + 0.05, lp0 + 0.02
+
+    def stats_step():
         # batch-level mean/std over ALL ranks + the global loss normaliser: one all-reduce
         if world > 1:
-            mean, denom, total_w = pkg.dist.global_advantage_stats(adv_raw, mask)
-        else:
-            mom = pkg.ops.masked_moments(adv_raw, mask.float(), n_tok, None, 1)
-            mean, denom = pkg.ops.moments_finalize(mom, False, False, 1e-5)
-            total_w = mom[0, 0:1]
+            return pkg.dist.global_advantage_stats(adv_raw, mask)
+        mom = pkg.ops.masked_moments(adv_raw, mask.float(), n_tok, None, 1)
+        mean, denom = pkg.ops.moments_finalize(mom, False, False, 1e-5)
+        return mean, denom, mom[0, 0:1]
+
+    def step():
+        mean, denom, total_w = stats_step()
         adv = ((adv_raw * mask - mean.float()) / denom.float()).float()
         tot = torch.zeros((), device=dev)
         for a, b in zip(bounds[:-1], bounds[1:]):
             x = buf[: b - a].detach().requires_grad_(True)
-            data = dict(input_ids=ids[a:b], logprobs=lp0[a:b] + 0.05, advantages=adv[a:b],
-                        loss_mask=mask[a:b], prox_logp=lp0[a:b] + 0.02)
-            loss = grpo_loss_fn(x, data, 1.0, 0.2, 0.28, 3.0, 5.0, stats={})
+            data = dict(input_ids=ids[a:b], logprobs=old_lp[a:b], advantages=adv[a:b],
+                        loss_mask=mask[a:b], prox_logp=prox_lp[a:b])
+            loss = grpo_loss_fn(x, data, 1.0, *CLIP, stats={})
             # the engine's scaling: local mask count / global count (fsdp_engine.py:543-547)
             (g,) = torch.autograd.grad(loss * (mask[a:b].sum() / total_w.float()), x)
             tot = tot + loss.detach()
@@ -447,14 +521,105 @@ def run_cfg4(dev, rank, world, steps=2):
         max_tok, ms, sum_tok = float(mx[0]), float(mx[1]), float(toks[0])
     else:
         max_tok, sum_tok = float(n_tok), float(n_tok)
+    rec = {"workload": "cfg4: 1,048,576 tokens, seqs 1k-16k, sharded by tokens at sequence granularity, "
+                       "V=152064, mb 32768 tok on a reused logits buffer, batch-level AdvNorm (1 all-reduce/"
+                       "step), eps_clip 0.2/0.28, c_clip 3, cap 5",
+           "scaling": "strong", "n_gpus": world, "tokens": sum_tok, "ms_per_step_max_over_ranks": ms,
+           "tokens_per_s": sum_tok / (ms * 1e-3), "imbalance_max_over_mean_tokens": max_tok / (sum_tok / world),
+           "per_gpu_frac_of_measured_peak_at_6V_on_busiest_rank": None}
+
+    parity = None
+    if check and world > 1:
+        # ---- untimed: one more sharded step, by pieces, keeping per-token results ----
+        mean, denom, total_w = stats_step()
+        adv = ((adv_raw * mask - mean.float()) / denom.float()).float()
+        logp_l, g_l = [], []
+        scaled_loss = torch.zeros((), device=dev, dtype=torch.float64)
+        for a, b in zip(bounds[:-1], bounds[1:]):
+            x = buf[: b - a].detach().requires_grad_(True)
+            lp, _, _, _ = Fn.gather_logprobs_entropy_minmax(x, torch.roll(ids[a:b], -1), 1.0)
+            lp.retain_grad()
+            loss, _ = Fn.ppo_actor_loss_fn(lp, prox_lp[a:b], old_lp[a:b], adv[a:b], CLIP[0], mask[a:b],
+                                           CLIP[1], CLIP[2], CLIP[3])
+            w = mask[a:b].sum() / total_w.float()
+            (loss * w).backward()
+            scaled_loss += (loss.detach() * w).double()
+            logp_l.append(lp.detach())
+            g_l.append(lp.grad.detach())
+            del x
+        logp_mine, g_mine = torch.cat(logp_l), torch.cat(g_l)
+        dist.all_reduce(scaled_loss)
+        parts = {k: _gather_var(v, world) for k, v in dict(
+            adv_raw=adv_raw, mask=mask.float(), ids=ids.double(), lp0=lp0, logp=logp_mine, g=g_mine, adv=adv).items()}
+        ok = torch.ones(1, device=dev)
+        if rank == 0:
+            cat = {k: torch.cat(v) for k, v in parts.items()}
+            m_all = cat["mask"] > 0
+            mom = pkg.ops.masked_moments(cat["adv_raw"].contiguous(), cat["mask"].contiguous(), cat["mask"].numel(), None, 1)
+            mean1, denom1 = pkg.ops.moments_finalize(mom, False, False, 1e-5)
+            adv1 = ((cat["adv_raw"] * cat["mask"] - mean1.float()) / denom1.float()).float()
+            lp_all = cat["logp"].clone().requires_grad_(True)
+            loss1, _ = Fn.ppo_actor_loss_fn(lp_all, cat["lp0"] + 0.02, cat["lp0"] + 0.05, adv1, CLIP[0], m_all,
+                                            CLIP[1], CLIP[2], CLIP[3])
+            loss1.backward()
+            rel = lambda x_, y_: float((x_ - y_).abs().max() / y_.abs().max().clamp_min(1e-30))
+            err = {"mean": float((mean - mean1).abs().max()), "denom_rel": rel(denom, denom1),
+                   "total_loss_weight": float((total_w.double() - mom[0, 0]).abs().max()),
+                   "adv_max_abs": float((cat["adv"] - adv1).abs().max()),
+                   "loss_rel": float(abs(scaled_loss.item() - loss1.item()) / max(abs(loss1.item()), 1e-30)),
+                   "g_logp_rel": rel(cat["g"], lp_all.grad)}
+            # another GPU's log-probs, recomputed here from its (regenerated) logits and gathered ids
+            worst = 0.0
+            for r in range(1, world):
+                rb = make_buf(r)
+                ids_r, lp_r = parts["ids"][r].long(), parts["logp"][r]
+                for a in range(0, ids_r.numel(), MB):
+                    b = min(a + MB, ids_r.numel())
+                    lp_here, _, _, _ = Fn.gather_logprobs_entropy_minmax(rb[: b - a], torch.roll(ids_r[a:b], -1), 1.0)
+                    worst = max(worst, float((lp_here - lp_r[a:b]).abs().max()))
+                del rb
+            err["logp_other_gpus_max_abs"] = worst
+            good = (err["mean"] <= 1e-5 and err["denom_rel"] <= 1e-5 and err["total_loss_weight"] == 0.0
+                    and err["adv_max_abs"] <= 1e-5 and err["loss_rel"] <= 1e-3 and err["g_logp_rel"] <= 1e-3
+                    and worst <= 1e-5)
+            ok[0] = float(good)
+            parity = {"ok": bool(good), "tokens": int(cat["mask"].numel()), "err": err,
+                      "bars": "mean/denom/adv 1e-5, loss and d loss/d logp 1e-3 rel, logp 1e-5"}
+        dist.broadcast(ok, src=0)
+        if rank != 0:
+            parity = {"ok": bool(ok.item() == 1.0)}
     del buf
     torch.cuda.empty_cache()
-    return {"workload": "cfg4: 1,048,576 tokens, seqs 1k-16k, groups of 8 sharded by tokens, V=152064, "
-                        "mb 32768 tok on a reused logits buffer, batch-level AdvNorm (1 all-reduce/step), "
-                        "eps_clip 0.2/0.28, c_clip 3, cap 5",
-            "scaling": "strong", "n_gpus": world, "tokens": sum_tok, "ms_per_step_max_over_ranks": ms,
-            "tokens_per_s": sum_tok / (ms * 1e-3), "imbalance_max_over_mean_tokens": max_tok / (sum_tok / world),
-            "per_gpu_frac_of_measured_peak_at_6V_on_busiest_rank": None}
+    return rec, parity
+
+
+def run_group_norm_parity(dev, rank, world):
+    """Group-level AdvNorm with the rows of a group on different ranks (sequence-granular
+    sharding) vs AdvNorm(group, group) on the whole batch (ref actor.py:412-470), cfg2 shape."""
+    import torch.distributed as dist
+
+    import areal_vllm_b200 as pkg
+    from areal_vllm_b200.actor import AdvNorm
+
+    seqlens, resp_starts, _, rewards = make_batch(seed=2)
+    L = max(seqlens)
+    pad_mask = torch.zeros(N_SEQ, L)
+    for i, (n, p) in enumerate(zip(seqlens, resp_starts)):
+        pad_mask[i, p - 1: n - 1] = 1.0
+    gen = torch.Generator().manual_seed(22)
+    adv_pad = ((torch.from_numpy((rewards - 0.5) * 10.0)[:, None] + 0.1 * torch.randn(N_SEQ, L, generator=gen))
+               * pad_mask).to(dev)
+    pad_mask = pad_mask.to(dev)
+    mine = torch.tensor(pkg.dist.shard_sequences_by_tokens(seqlens, world)[rank], device=dev, dtype=torch.int64)
+    out, = pkg.dist.sharded_group_advantage_norm(adv_pad[mine], pad_mask[mine], mine // GROUP, N_SEQ // GROUP)
+
+    class Cfg:
+        mean_level, std_level, group_size = "group", "group", GROUP
+
+    full = AdvNorm(Cfg)(adv_pad, pad_mask)
+    err = torch.tensor([float((out - full[mine]).abs().max())], device=dev)
+    dist.all_reduce(err, op=dist.ReduceOp.MAX)
+    return {"ok": bool(err.item() <= 1e-5), "max_abs_err": float(err.item()), "rows": N_SEQ, "groups": N_SEQ // GROUP}
 
 
 # ------------------------------------------------------------------------------------------
@@ -759,16 +924,40 @@ def main_b200rl(args):
         extras = {"gae_weak_scaling_65536_seqs_per_rank": res}
         del r_, v_, cu_, b_
     cfg4 = None
+    parity = None
     if not args.no_extras:  # every rank takes part (one all-reduce per step)
         del logits_bufs[:]
         torch.cuda.empty_cache()
         try:
-            cfg4 = run_cfg4(dev, rank, world)
+            cfg4, sharded = run_cfg4(dev, rank, world, check=not args.no_parity)
             cfg4["per_gpu_frac_of_measured_peak_at_6V_on_busiest_rank"] = (
                 cfg4["imbalance_max_over_mean_tokens"] * cfg4["tokens"] / world * 6 * 152064
                 / (cfg4["ms_per_step_max_over_ranks"] * 1e-3) / 1e9 / peak)
         except Exception as e:  # must not cost the headline line
-            cfg4 = {"error": repr(e)[:300]}
+            cfg4, sharded = {"error": repr(e)[:300]}, {"ok": False, "error": repr(e)[:300]}
+        if world > 1 and not args.no_parity:
+            # ---- N >= 2: correctness of every cross-GPU path, after the timed regions ----
+            # sharded_step: the data-parallel arithmetic of the cfg4 step (see run_cfg4);
+            # group_norm: group-level AdvNorm with a group's rows on different ranks;
+            # tp: vocabulary-parallel log-prob/entropy over NCCL with tp = world vs the whole-
+            #     vocabulary kernel (ref mcore/functional.py:8-52);
+            # peer_move: move_intervals reading rank 0's flat buffer over NVLink vs slice ->
+            #     NCCL broadcast -> set (ref real_llm_api.py:721-805), bit-exact.
+            sys.path.insert(0, os.path.join(ROOT, "scripts"))
+            import p2p_move_check
+            import tp_check
+
+            details = {"sharded_step": sharded}
+            for name, fn in (("group_norm", lambda: run_group_norm_parity(dev, rank, world)),
+                             ("tp", lambda: tp_check.run(dev, rank, world, T=2048)),
+                             ("peer_move", lambda: p2p_move_check.run(dev, rank, world, scale=0.25))):
+                try:
+                    details[name] = fn()
+                except Exception as e:
+                    details[name] = {"ok": False, "error": repr(e)[:300]}
+                torch.cuda.empty_cache()
+            parity = {k: bool(v and v.get("ok")) for k, v in details.items()}
+            parity["details"] = details
     if rank == 0 and world == 1 and not args.no_extras:
         extras = run_extras(dev, peak, args.compiled_baseline)
     if extras is not None:
@@ -786,7 +975,7 @@ def main_b200rl(args):
                        "cache": f"inputs larger than L2: {N_LOGITS_BUFFERS} rotating logits buffers of "
                                 f"{max_T}x{V} bf16 = {max_T * V * 2 / 1e9:.2f} GB each"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "clocks": clocks,
-            "fused_step": fused, "extra": extras,
+            "fused_step": fused, "strong_scaling": cfg4, "parity": parity, "extra": extras,
             "gpu_launches": args.steps * (3 + 4 * n_mb),
             "gpu_launches_note": "per step: masked_moments+moments_finalize+masked_normalize, then per "
                                  "micro-batch logprob_fwd, ppo_loss_fwd, ppo_loss_bwd, logprob_bwd",
@@ -794,6 +983,8 @@ def main_b200rl(args):
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and not all(v for k, v in parity.items() if k != "details"):
+        sys.exit(3)  # a cross-GPU path disagreed with its single-GPU computation: the line says which
 
 
 def main():
@@ -808,6 +999,7 @@ def main():
     ap.add_argument("--compiled-baseline", action="store_true",
                     help="extras: also time the torch.compile'd torch GPU path (adds Inductor compile time)")
     ap.add_argument("--no-fused", action="store_true", help="skip the fused-step extension measurement")
+    ap.add_argument("--no-parity", action="store_true", help="N >= 2: skip the cross-GPU parity block")
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)

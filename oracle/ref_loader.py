@@ -1,7 +1,10 @@
-"""Loads the REAL reference functions from /root/reference (build container only).
-TEST INFRASTRUCTURE: used by gen_golden.py to produce tests/golden/*, and by
-tests/test_reference_live.py when the tree is present. Nothing under -m gpu, smoke() or
-bench.py touches this module (/root/reference does not exist on the GPU box).
+"""Loads the REAL reference functions from a reference tree: $B200RL_REFERENCE, /root/reference
+(build container only) or <repo>/baseline/_ref (the `pip install --target` copy of the reference's
+`areal` package, git-ignored, which travels to the GPU box with the snapshot; SURVEY §8c note 2).
+TEST INFRASTRUCTURE: used by gen_golden.py to produce tests/golden/*, by
+tests/test_reference_live.py when a tree is present, and by the CPU-baseline / --impl reference
+legs of bench.py (which time the reference's own functions when a tree is found and fall back to
+the oracle port, saying so, when none is). Nothing under -m gpu or smoke() touches this module.
 
 No reference source is copied: modules are imported from where they lie, with stub modules for
 the dependencies that are absent here (tensordict, omegaconf-based realhf.base).
@@ -15,11 +18,29 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("B200RL_REFERENCE", "/root/reference")
+_REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _find_root() -> str:
+    cands = [os.environ.get("B200RL_REFERENCE"), "/root/reference", os.path.join(_REPO, "baseline", "_ref")]
+    for c in cands:
+        if c and os.path.isfile(os.path.join(c, "areal", "utils", "functional.py")):
+            return c
+    return os.environ.get("B200RL_REFERENCE", "/root/reference")
+
+
+REF_ROOT = _find_root()
 
 
 def available() -> bool:
-    return os.path.isdir(os.path.join(REF_ROOT, "areal"))
+    """The reference's `areal` package (H1/H2, AdvNorm, SFT loss) can be loaded."""
+    return os.path.isfile(os.path.join(REF_ROOT, "areal", "utils", "functional.py"))
+
+
+def realhf_available() -> bool:
+    """The legacy `realhf` tree (pygae, actor_loss_fn, interval python fallbacks) is present:
+    only in a full checkout, the pip-installed package excludes it (pyproject.toml:165-168)."""
+    return os.path.isfile(os.path.join(REF_ROOT, "realhf", "impl", "model", "utils", "ppo_functional.py"))
 
 
 def areal_functional():

@@ -262,3 +262,41 @@ def test_padded_rows_get_exact_zero_gradient(cuda):
     assert torch.equal(la, lb)
     assert torch.equal(b.grad[:T], a.grad)
     assert int((b.grad[T:].view(torch.int16) & 0x7fff).max()) == 0  # +-0 only
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_sharded_group_advantage_norm_matches_advnorm(world, cuda):
+    """Rows of one GRPO group on different ranks (sequence-granular sharding): the [G, 3] moment
+    tables of the simulated ranks are summed (what the all-reduce does) and every rank's rows must
+    equal AdvNorm(group, group) on the whole batch (ref actor.py:412-470)."""
+    from areal_vllm_b200 import dist as bdist
+    from areal_vllm_b200.actor import AdvNorm
+
+    gen = torch.Generator().manual_seed(5)
+    B, L, gs = 64, 96, 8
+    lens = torch.randint(4, L + 1, (B,), generator=gen)
+    mask = (torch.arange(L)[None, :] < lens[:, None]).float()
+    adv = torch.randn(B, L, generator=gen) * 3 + 1
+    adv, mask = adv.to(cuda), mask.to(cuda)
+
+    class Cfg:
+        mean_level, std_level, group_size = "group", "group", gs
+
+    for unbiased in (False, True):
+        full = AdvNorm(Cfg)(adv, mask, unbiased=unbiased)
+        parts = bdist.shard_sequences_by_tokens(lens.tolist(), world)
+        idx = [torch.tensor(p, device=cuda, dtype=torch.int64) for p in parts]
+        tables = []
+        for r in range(world):  # pass 1: every rank's local table
+            bdist.sharded_group_advantage_norm(adv[idx[r]], mask[idx[r]], idx[r] // gs, B // gs, unbiased=unbiased,
+                                               reduce=lambda t, *e: (tables.append(t.clone()) or (t,) + e))
+        total = torch.stack(tables).sum(0)
+        for r in range(world):  # pass 2: with the summed table, as after the all-reduce
+            out, extra = bdist.sharded_group_advantage_norm(
+                adv[idx[r]], mask[idx[r]], idx[r] // gs, B // gs, unbiased=unbiased,
+                extra=(torch.ones(1, device=cuda),), reduce=lambda t, *e: (total,) + e)
+            assert extra.item() == 1.0
+            if len(parts[r]):
+                torch.testing.assert_close(out, full[idx[r]], rtol=1e-5, atol=1e-5)
+            else:
+                assert out.shape == (0, L)

@@ -9,6 +9,7 @@ import torch
 from oracle import cpu_ref, ref_loader as R, torch_ref
 
 pytestmark = pytest.mark.skipif(not R.available(), reason="reference tree not present")
+needs_realhf = pytest.mark.skipif(not R.realhf_available(), reason="realhf tree not present (pip-installed areal only)")
 
 
 @pytest.mark.parametrize("seed", range(4))
@@ -39,6 +40,7 @@ def test_h1_h2_fuzz(seed):
         assert torch.equal(s_r[k], s_o[k]), k
 
 
+@needs_realhf
 @pytest.mark.parametrize("seed", range(3))
 def test_gae_fuzz(seed):
     P = R.realhf_ppo_functional()
@@ -74,6 +76,7 @@ def test_advnorm_fuzz():
             assert torch.equal(ref, out), (m, s)
 
 
+@needs_realhf
 def test_intervals_and_merge_fuzz():
     fp = R.flatten_param_py()
     merge_ref = R.merge_intervals_ext()
@@ -97,6 +100,7 @@ def test_intervals_and_merge_fuzz():
         assert cpu_ref.merge_intervals(pairs) == merge_ref(pairs)
 
 
+@needs_realhf
 @pytest.mark.parametrize("seed", range(4))
 def test_critic_rewards_fuzz(seed):
     P = R.realhf_ppo_functional()
