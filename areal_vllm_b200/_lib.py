@@ -44,6 +44,22 @@ SIGNATURES = {
         [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
          c_int64, c_int64, c_float, c_void_p, c_int64, c_void_p],
     ),
+    "b200rl_grpo_loss_workspace_bytes": (c_size_t, [c_int64]),
+    "b200rl_grpo_loss_fwd": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_void_p, c_int, c_int64, c_int64, c_float,   # logits..temperature
+         c_void_p, c_void_p, c_void_p, c_void_p, c_int,                          # prox, old, adv, mask, mask_is_f32
+         c_float, c_float, c_float, c_float,                                     # clip_lo/hi, c_clip, cap
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,                       # logp, entropy, lse, rowmax, rowmin
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,  # 8 stats
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,                       # valid, 2 ratios, 2 clipped logp
+         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],            # dlogp, loss, denom, ws, stream
+    ),
+    "b200rl_grpo_loss_bwd": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_void_p, c_int, c_int64, c_int64, c_float,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p],
+    ),
     "b200rl_grpo_fused_workspace_bytes": (c_size_t, [c_int64]),
     "b200rl_grpo_fused_step": (
         c_int,
@@ -128,6 +144,11 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p,
          c_void_p],
+    ),
+    "b200rl_masked_normalize_groups": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_void_p, c_size_t, c_void_p],
     ),
     "b200rl_interval_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "b200rl_slice_intervals": (

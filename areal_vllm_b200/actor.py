@@ -25,6 +25,11 @@ __all__ = [
 ]
 
 
+# grpo_loss_fn: take the two-launch composite (csrc/grpo_loss.cu) in eager mode. Tests set this to
+# False to compare it against the custom-op path, which is what a compiled graph uses.
+FAST_PATH = True
+
+
 @torch.no_grad()
 def padded_gae(
     rewards: torch.Tensor,
@@ -127,6 +132,9 @@ class AdvNorm:
             if x.numel() == 0:
                 return x
             ge = x.numel() // G
+            if not torch.compiler.is_compiling():  # moments -> finalize -> normalise in one host call
+                return ops._raw_masked_normalize_groups(
+                    x.view(-1), None if m is None else m.view(-1), ge, bool(unbiased), float(eps)).view(x.shape)
             mom = ops.masked_moments(x.view(-1), None if m is None else m.view(-1), ge, None, 1)
             mean, denom = ops.moments_finalize(mom, False, bool(unbiased), float(eps))
             return ops.masked_normalize(
@@ -138,6 +146,13 @@ class AdvNorm:
         m = None if loss_mask is None else loss_mask.to(torch.float32).contiguous()
         n = x.numel()
         if n == 0:
+            # keep an empty data-parallel shard in step with the others: one zero-moment
+            # all-reduce per batch-level statistic, in the order the non-empty ranks issue them
+            if dist.is_initialized():
+                for level in (self.mean_level, self.std_level):
+                    if level == "batch":
+                        dist.all_reduce(torch.zeros(1, 3, dtype=torch.float64, device=x.device),
+                                        op=dist.ReduceOp.SUM, group=reduce_group)
             return x
         xf = x.view(-1)
         mf = None if m is None else m.view(-1)
@@ -387,9 +402,42 @@ def grpo_loss_fn(
     input_ids = input_data["input_ids"]
     old_logp = input_data["logprobs"]
     advantages = input_data["advantages"]
-    loss_mask = input_data["loss_mask"].bool()
     prox_logp = input_data["prox_logp"]
+    st = _stats_tracker()
+    want_stats = stats is not None or st is not None
 
+    if (FAST_PATH and logits.is_cuda and logits.dim() == 2 and input_ids.dim() == 1 and input_ids.dtype == torch.int64
+            and input_ids.is_contiguous() and logits.stride(1) == 1 and logits.dtype in _lib_dtypes()
+            and not torch.compiler.is_compiling()):
+        # eager fast path: the whole function is TWO launches (log-prob forward with the label roll
+        # as an index computation; loss kernel that reads the engine's float mask as it is and
+        # writes every logged tensor), its backward ONE (csrc/grpo_loss.cu). Nobody consumes the
+        # logging tensors -> entropy and row min/max are not even computed.
+        if c_clip is not None:
+            assert c_clip > 1.0, c_clip
+        loss, r = ops.grpo_loss(
+            logits, input_ids, True, prox_logp, old_logp, advantages, input_data["loss_mask"],
+            float(temperature), 1.0 - eps_clip, 1.0 + (eps_clip if eps_clip_higher is None else eps_clip_higher),
+            -1.0 if c_clip is None else float(c_clip),
+            -1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap), want_stats)
+        if not want_stats:
+            return loss
+        collected = dict(
+            n_valid_tokens=r["valid"], clipped_tokens=r["s_clip"], dual_clipped_tokens=r["s_dual"],
+            importance_weight=r["s_iw"], approx_kl=r["s_kl"], new_logp=r["logp"], old_logp=old_logp,
+            entropy=r["entropy"], actor_loss=r["s_loss"], clip_ratio=r["clip_ratio"],
+            dual_clip_ratio=r["dual_clip_ratio"], unclipped_behave_tokens=r["s_bm"],
+            behave_imp_weight=r["s_bw"], behave_approx_kl=r["s_bkl"], vocab_min_logits=r["rowmin"],
+            vocab_max_logits=r["rowmax"], clipped_new_logp=r["clipped_new_logp"],
+            clipped_old_logp=r["clipped_old_logp"],
+        )
+        if stats is not None:
+            stats.update(collected)
+        _register_stats(st, logits, collected)
+        return loss
+
+    # custom-op path (torch.compile, leading batch dims, int32 ids, ...)
+    loss_mask = input_data["loss_mask"].bool()
     labels = torch.roll(input_ids, shifts=-1, dims=-1)
     logprobs, entropy, vmax, vmin = functional.gather_logprobs_entropy_minmax(
         logits, labels, temperature
@@ -406,8 +454,7 @@ def grpo_loss_fn(
         proximal_logprobs=prox_logp,
         behav_imp_weight_cap=behav_imp_weight_cap,
     )
-    st = _stats_tracker()
-    if stats is None and st is None:
+    if not want_stats:
         return loss  # nobody consumes the logging tensors: do not launch the derived ones
     clip_mask = stat["clip_mask"]
     new_logp = logprobs.detach()
@@ -435,3 +482,9 @@ def grpo_loss_fn(
         stats.update(collected)
     _register_stats(st, logits, collected)
     return loss
+
+
+def _lib_dtypes():
+    from . import _lib
+
+    return _lib.DTYPE_CODE

@@ -203,4 +203,18 @@ int b200rl_masked_normalize(const float* x, const float* mask, int64_t n_elems,
   return check_launch("masked_normalize_kernel");
 }
 
+int b200rl_masked_normalize_groups(const float* x, const float* mask, int64_t n_elems,
+                                   int64_t group_elems, int unbiased, double eps, float* out,
+                                   double* moments, double* mean, double* denom, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+  using namespace b200rl;
+  B200RL_REQUIRE(n_elems == 0 || (moments && mean && denom), "moments/mean/denom must not be null");
+  int rc = b200rl_masked_moments(x, mask, n_elems, group_elems, nullptr, 1, moments, workspace,
+                                 workspace_bytes, stream);
+  if (rc || n_elems == 0) return rc;
+  rc = b200rl_moments_finalize(moments, n_elems / group_elems, 0, unbiased, eps, mean, denom, stream);
+  if (rc) return rc;
+  return b200rl_masked_normalize(x, mask, n_elems, mean, group_elems, denom, group_elems, 1, out, stream);
+}
+
 }  // extern "C"

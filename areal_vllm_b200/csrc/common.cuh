@@ -45,6 +45,42 @@ inline int check_launch(const char* what) {
 
 int sm_count();  // SM count of the current device (cached per device)
 
+// ---- launchers shared between translation units (not part of the C ABI) ----------------------
+// logprob.cu. `roll` != 0: `labels` is the packed input_ids, row t's label is labels[(t+1) % T].
+// bwd: when g_num is non-null the per-row upstream gradient is g_logp[t] * (g_num[0] / g_den[0]).
+int logprob_fwd_impl(const void* logits, int dtype, int64_t ld, const int64_t* labels, int64_t T,
+                     int64_t V, float temperature, float* logp, float* entropy, float* lse,
+                     float* rowmax, float* rowmin, float* partial, bool want_ent, bool want_mm,
+                     int roll, void* stream);
+int logprob_bwd_impl(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                     const float* lse, const float* entropy, const float* g_logp,
+                     const float* g_ent, int64_t T, int64_t V, float temperature, void* dlogits,
+                     int64_t ld_out, int roll, const float* g_num, const float* g_den,
+                     void* stream);
+
+// ppo_loss.cu: everything b200rl_ppo_loss_fwd takes, plus an fp32 mask alternative and the
+// derived logging tensors of grpo_loss_fn (areal/engine/ppo/actor.py:339-365).
+struct PpoLossArgs {
+  const float *logp, *prox, *old, *adv;
+  const uint8_t* mask;     // bytes (torch.bool) ...
+  const float* mask_f32;   // ... or fp32 (non-zero = valid) when mask == nullptr
+  int64_t T;
+  float clip_lo, clip_hi, c_clip, cap;
+  const double *adv_mean, *adv_denom;
+  const int32_t* adv_group;
+  float* adv_out;
+  float *s_loss, *s_iw, *s_kl;
+  uint8_t *s_clip, *s_dual;
+  float *s_bw, *s_bkl;
+  uint8_t* s_bm;
+  // extras (all nullable): the mask as bytes, clip_mask / dual_clip_mask as fp32, and
+  // where(clip_mask, logp, 0) / where(clip_mask, old_logp, 0)
+  uint8_t* s_valid;
+  float *s_clip_ratio, *s_dual_ratio, *s_clip_new, *s_clip_old;
+  float *dlogp, *loss, *denom;
+};
+int ppo_loss_fwd_launch(const PpoLossArgs& a, void* workspace, size_t workspace_bytes, void* stream);
+
 // ---- small PTX wrappers ---------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

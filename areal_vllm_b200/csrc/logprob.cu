@@ -30,6 +30,12 @@ using namespace lp;
 // floats per row of the vocabulary-shard partial record: (M, S, W, x_y, max, min, 0, 0)
 constexpr int kPartialStride = 8;
 
+// roll != 0: `labels` holds the packed input_ids and the label of row t is the NEXT token,
+// labels[(t + 1) % T] = torch.roll(input_ids, -1)[t] (ref areal/engine/ppo/actor.py:308)
+__device__ __forceinline__ int label_row(int row, int T, int roll) {
+  return roll ? (row + 1 == T ? 0 : row + 1) : row;
+}
+
 // ------------------------------------------------------------------------------------------
 // forward, rows 16-B aligned (bf16 / fp16 / fp32)
 // ------------------------------------------------------------------------------------------
@@ -39,7 +45,7 @@ logprob_fwd_kernel(const void* __restrict__ logits, int64_t ld,
                         const int64_t* __restrict__ labels, int T, int V, float scale,
                         float* __restrict__ logp, float* __restrict__ ent,
                         float* __restrict__ lse, float* __restrict__ rowmax,
-                        float* __restrict__ rowmin, float* __restrict__ partial) {
+                        float* __restrict__ rowmin, float* __restrict__ partial, int roll) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FwdSmem<WARPS, STAGES>;
   using E = Elem<DT>;
@@ -62,7 +68,7 @@ logprob_fwd_kernel(const void* __restrict__ logits, int64_t ld,
     float xy = 0.f;
     const bool fetch_xy = (it % WARPS) == warp && lane == 0;
     if (fetch_xy) {
-      const int64_t lab = labels[row];
+      const int64_t lab = labels[label_row(row, T, roll)];
       xy = (lab >= 0 && lab < V) ? E::load1(logits, (int64_t)row * ld + lab)
                                  : __int_as_float(0x7fc00000);
     }
@@ -195,7 +201,8 @@ logprob_bwd_kernel(const void* __restrict__ logits, int64_t ld,
                         const int64_t* __restrict__ labels, const float* __restrict__ lse,
                         const float* __restrict__ entropy, const float* __restrict__ g_logp,
                         const float* __restrict__ g_ent, int T, int V, float scale,
-                        float inv_temp, void* __restrict__ dlogits, int64_t ld_out) {
+                        float inv_temp, void* __restrict__ dlogits, int64_t ld_out, int roll,
+                        const float* __restrict__ g_num, const float* __restrict__ g_den) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = FwdSmem<WARPS, STAGES>;
   using E = Elem<DT>;
@@ -207,10 +214,13 @@ logprob_bwd_kernel(const void* __restrict__ logits, int64_t ld,
           reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
   if (ws.seg_len == 0) return;  // this warp owns no part of the row (tiny vocabularies)
 
+  // g_logp scaled by g_num[0] / g_den[0] when given: the scalar loss's backward
+  // (ppo_loss_bwd_kernel's `dlogp[t] * (grad_loss / N)`, same operation order) folded in
+  const float gs = g_num ? g_num[0] / g_den[0] : 1.f;
   // per-row constants, fetched one row ahead
   auto load_row = [&](int row, float& nlse2, float& A0, float& B0, float& lab_add, int& lvec,
                       int& lsub) {
-    const float glp = g_logp[row];
+    const float glp = g_num ? g_logp[row] * gs : g_logp[row];
     nlse2 = -lse[row] * kLog2e;
     float gh = 0.f, H = 0.f;
     if (HAS_GH) {
@@ -220,7 +230,7 @@ logprob_bwd_kernel(const void* __restrict__ logits, int64_t ld,
     A0 = -(glp + gh * H) * inv_temp;
     B0 = -gh * kLn2 * inv_temp;
     lab_add = glp * inv_temp;
-    const int64_t lab = labels[row];
+    const int64_t lab = labels[label_row(row, T, roll)];
     const bool ok = lab >= 0 && lab < V;
     lvec = ok ? (int)(lab / E::kPerVec) : -1;
     lsub = (int)(lab % E::kPerVec);
@@ -297,7 +307,7 @@ __global__ void __launch_bounds__(kPlainThreads)
 logprob_fwd_plain_kernel(const T* __restrict__ logits, int64_t ld, const int64_t* __restrict__ labels,
                          int64_t V, float scale, float* __restrict__ logp, float* __restrict__ ent,
                          float* __restrict__ lse, float* __restrict__ rowmax,
-                         float* __restrict__ rowmin, float* __restrict__ partial) {
+                         float* __restrict__ rowmin, float* __restrict__ partial, int roll) {
   __shared__ float sh[kPlainThreads / 32];
   const int64_t row = blockIdx.x;
   const T* x = logits + row * ld;
@@ -322,7 +332,7 @@ logprob_fwd_plain_kernel(const T* __restrict__ logits, int64_t ld, const int64_t
   if (threadIdx.x == 0) {
     const float l2s = log2f(s);
     const float lse2 = m2 + l2s;
-    const int64_t lab = labels[row];
+    const int64_t lab = labels[label_row((int)row, (int)gridDim.x, roll)];
     const float xy = (lab >= 0 && lab < V) ? to_f<T>(x[lab]) : __int_as_float(0x7fc00000);
     if (partial) {
       float4* pr = reinterpret_cast<float4*>(partial + row * kPartialStride);
@@ -344,17 +354,18 @@ logprob_bwd_plain_kernel(const T* __restrict__ logits, int64_t ld, const int64_t
                          const float* __restrict__ lse, const float* __restrict__ entropy,
                          const float* __restrict__ g_logp, const float* __restrict__ g_ent,
                          int64_t V, float scale, float inv_temp, T* __restrict__ dlogits,
-                         int64_t ld_out) {
+                         int64_t ld_out, int roll, const float* __restrict__ g_num,
+                         const float* __restrict__ g_den) {
   const int64_t row = blockIdx.x;
   const T* x = logits + row * ld;
   T* o = dlogits + row * ld_out;
-  const float glp = g_logp[row];
+  const float glp = g_num ? g_logp[row] * (g_num[0] / g_den[0]) : g_logp[row];
   const float gh = g_ent ? g_ent[row] : 0.f;
   const float H = g_ent ? entropy[row] : 0.f;
   const float nlse2 = -lse[row] * kLog2e;
   const float A0 = -(glp + gh * H) * inv_temp;
   const float B0 = -gh * kLn2 * inv_temp;
-  const int64_t lab = labels[row];
+  const int64_t lab = labels[label_row((int)row, (int)gridDim.x, roll)];
   for (int64_t j = threadIdx.x; j < V; j += kPlainThreads) {
     const float y = fmaf(to_f<T>(x[j]), scale, nlse2);
     float d = exp2f(y) * fmaf(B0, y, A0);
@@ -446,64 +457,66 @@ logprob_shard_combine_kernel(const float* __restrict__ partials, int n_shards, i
 template <int DT, bool ENT, bool MINMAX>
 int launch_fwd_fast(const void* logits, int64_t ld, const int64_t* labels, int T, int V,
                     float scale, float* logp, float* ent, float* lse, float* rowmax,
-                    float* rowmin, float* partial, cudaStream_t st) {
+                    float* rowmin, float* partial, int roll, cudaStream_t st) {
   auto k = logprob_fwd_kernel<DT, kFwdWarps, kFwdStages, ENT, MINMAX>;
   constexpr int smem = FwdSmem<kFwdWarps, kFwdStages>::kBytes;
   int rc = set_smem(k, smem);
   if (rc) return rc;
   const int grid = min(T, sm_count());
   k<<<grid, kFwdWarps * 32, smem, st>>>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin,
-                                        partial);
+                                        partial, roll);
   return check_launch("logprob_fwd_kernel");
 }
 
 template <int DT>
 int dispatch_fwd_fast(const void* logits, int64_t ld, const int64_t* labels, int T, int V,
                       float scale, float* logp, float* ent, float* lse, float* rowmax,
-                      float* rowmin, float* partial, bool want_ent, bool want_mm, cudaStream_t st) {
+                      float* rowmin, float* partial, bool want_ent, bool want_mm, int roll,
+                      cudaStream_t st) {
   if (want_ent) {
-    return want_mm ? launch_fwd_fast<DT, true, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st)
-                   : launch_fwd_fast<DT, true, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st);
+    return want_mm ? launch_fwd_fast<DT, true, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, roll, st)
+                   : launch_fwd_fast<DT, true, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, roll, st);
   }
-  return want_mm ? launch_fwd_fast<DT, false, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st)
-                 : launch_fwd_fast<DT, false, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, st);
+  return want_mm ? launch_fwd_fast<DT, false, true>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, roll, st)
+                 : launch_fwd_fast<DT, false, false>(logits, ld, labels, T, V, scale, logp, ent, lse, rowmax, rowmin, partial, roll, st);
 }
 
 template <int DT, bool HAS_GH>
 int launch_bwd_fast(const void* logits, int64_t ld, const int64_t* labels, const float* lse,
                     const float* entropy, const float* g_logp, const float* g_ent, int T, int V,
-                    float scale, float inv_temp, void* dlogits, int64_t ld_out, cudaStream_t st) {
+                    float scale, float inv_temp, void* dlogits, int64_t ld_out, int roll,
+                    const float* g_num, const float* g_den, cudaStream_t st) {
   auto k = logprob_bwd_kernel<DT, kBwdWarps, kBwdStages, HAS_GH>;
   constexpr int smem = FwdSmem<kBwdWarps, kBwdStages>::kBytes;
   int rc = set_smem(k, smem);
   if (rc) return rc;
   const int grid = min(T, sm_count());
   k<<<grid, kBwdWarps * 32, smem, st>>>(logits, ld, labels, lse, entropy, g_logp, g_ent, T, V, scale,
-                                     inv_temp, dlogits, ld_out);
+                                     inv_temp, dlogits, ld_out, roll, g_num, g_den);
   return check_launch("logprob_bwd_kernel");
 }
 
 template <int DT>
 int dispatch_bwd_fast(const void* logits, int64_t ld, const int64_t* labels, const float* lse,
                       const float* entropy, const float* g_logp, const float* g_ent, int T, int V,
-                      float scale, float inv_temp, void* dlogits, int64_t ld_out, cudaStream_t st) {
+                      float scale, float inv_temp, void* dlogits, int64_t ld_out, int roll,
+                      const float* g_num, const float* g_den, cudaStream_t st) {
   return g_ent ? launch_bwd_fast<DT, true>(logits, ld, labels, lse, entropy, g_logp, g_ent, T, V, scale,
-                                           inv_temp, dlogits, ld_out, st)
+                                           inv_temp, dlogits, ld_out, roll, g_num, g_den, st)
                : launch_bwd_fast<DT, false>(logits, ld, labels, lse, entropy, g_logp, g_ent, T, V, scale,
-                                            inv_temp, dlogits, ld_out, st);
+                                            inv_temp, dlogits, ld_out, roll, g_num, g_den, st);
 }
 
 inline int per_vec(int dtype) { return dtype == B200RL_FP32 ? 4 : 8; }
 
 }  // namespace
-}  // namespace b200rl
 
-// shared by the whole-vocabulary forward and the vocabulary-shard (partial) forward
-static int logprob_fwd_impl(const void* logits, int dtype, int64_t ld, const int64_t* labels,
-                            int64_t T, int64_t V, float temperature, float* logp, float* entropy,
-                            float* lse, float* rowmax, float* rowmin, float* partial, bool want_ent,
-                            bool want_mm, void* stream) {
-  using namespace b200rl;
+// shared by the whole-vocabulary forward, the vocabulary-shard (partial) forward and the
+// grpo_loss composite (grpo_loss.cu); declared in common.cuh
+int logprob_fwd_impl(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                     int64_t T, int64_t V, float temperature, float* logp, float* entropy,
+                     float* lse, float* rowmax, float* rowmin, float* partial, bool want_ent,
+                     bool want_mm, int roll, void* stream) {
   B200RL_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
   B200RL_REQUIRE(ld >= V, "row stride %lld < V %lld", (long long)ld, (long long)V);
   B200RL_REQUIRE(temperature > 0.f, "temperature must be > 0, got %f", temperature);
@@ -521,26 +534,26 @@ static int logprob_fwd_impl(const void* logits, int dtype, int64_t ld, const int
   if (fast) {
     switch (dtype) {
       case B200RL_BF16:
-        return dispatch_fwd_fast<B200RL_BF16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, st);
+        return dispatch_fwd_fast<B200RL_BF16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, roll, st);
       case B200RL_FP16:
-        return dispatch_fwd_fast<B200RL_FP16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, st);
+        return dispatch_fwd_fast<B200RL_FP16>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, roll, st);
       default:
-        return dispatch_fwd_fast<B200RL_FP32>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, st);
+        return dispatch_fwd_fast<B200RL_FP32>(logits, ld, labels, (int)T, (int)V, scale, logp, entropy, lse, rowmax, rowmin, partial, want_ent, want_mm, roll, st);
     }
   }
   const unsigned grid = (unsigned)T;
   switch (dtype) {
     case B200RL_BF16:
       logprob_fwd_plain_kernel<__nv_bfloat16><<<grid, kPlainThreads, 0, st>>>(
-          (const __nv_bfloat16*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial);
+          (const __nv_bfloat16*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial, roll);
       break;
     case B200RL_FP16:
       logprob_fwd_plain_kernel<__half><<<grid, kPlainThreads, 0, st>>>(
-          (const __half*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial);
+          (const __half*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial, roll);
       break;
     case B200RL_FP32:
       logprob_fwd_plain_kernel<float><<<grid, kPlainThreads, 0, st>>>(
-          (const float*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial);
+          (const float*)logits, ld, labels, V, scale, logp, entropy, lse, rowmax, rowmin, partial, roll);
       break;
     default:
       set_last_error("unsupported logits dtype code %d", dtype);
@@ -549,15 +562,17 @@ static int logprob_fwd_impl(const void* logits, int dtype, int64_t ld, const int
   return check_launch("logprob_fwd_plain_kernel");
 }
 
+}  // namespace b200rl
+
 extern "C" {
 
 int b200rl_logprob_entropy_fwd(const void* logits, int dtype, int64_t ld, const int64_t* labels,
                                int64_t T, int64_t V, float temperature, float* logp,
                                float* entropy, float* lse, float* rowmax, float* rowmin,
                                void* stream) {
-  return logprob_fwd_impl(logits, dtype, ld, labels, T, V, temperature, logp, entropy, lse, rowmax,
-                          rowmin, nullptr, entropy != nullptr, rowmax != nullptr || rowmin != nullptr,
-                          stream);
+  return b200rl::logprob_fwd_impl(logits, dtype, ld, labels, T, V, temperature, logp, entropy, lse,
+                                  rowmax, rowmin, nullptr, entropy != nullptr,
+                                  rowmax != nullptr || rowmin != nullptr, 0, stream);
 }
 
 int b200rl_logprob_shard_fwd(const void* logits, int dtype, int64_t ld, const int64_t* local_labels,
@@ -566,7 +581,7 @@ int b200rl_logprob_shard_fwd(const void* logits, int dtype, int64_t ld, const in
   using namespace b200rl;
   B200RL_REQUIRE(partial || T == 0, "partial must not be null");
   return logprob_fwd_impl(logits, dtype, ld, local_labels, T, V_shard, temperature, nullptr, nullptr,
-                          nullptr, nullptr, nullptr, partial, need_entropy != 0, need_minmax != 0,
+                          nullptr, nullptr, nullptr, partial, need_entropy != 0, need_minmax != 0, 0,
                           stream);
 }
 
@@ -590,7 +605,19 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
                                const float* lse, const float* entropy, const float* g_logp,
                                const float* g_ent, int64_t T, int64_t V, float temperature,
                                void* dlogits, int64_t ld_out, void* stream) {
-  using namespace b200rl;
+  return b200rl::logprob_bwd_impl(logits, dtype, ld, labels, lse, entropy, g_logp, g_ent, T, V,
+                                  temperature, dlogits, ld_out, 0, nullptr, nullptr, stream);
+}
+
+}  // extern "C"
+
+namespace b200rl {
+
+int logprob_bwd_impl(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                     const float* lse, const float* entropy, const float* g_logp,
+                     const float* g_ent, int64_t T, int64_t V, float temperature, void* dlogits,
+                     int64_t ld_out, int roll, const float* g_num, const float* g_den,
+                     void* stream) {
   B200RL_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
   B200RL_REQUIRE(ld >= V && ld_out >= V, "row stride < V");
   B200RL_REQUIRE(temperature > 0.f, "temperature must be > 0, got %f", temperature);
@@ -610,11 +637,11 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
   if (fast) {
     switch (dtype) {
       case B200RL_BF16:
-        return dispatch_bwd_fast<B200RL_BF16>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, st);
+        return dispatch_bwd_fast<B200RL_BF16>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, roll, g_num, g_den, st);
       case B200RL_FP16:
-        return dispatch_bwd_fast<B200RL_FP16>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, st);
+        return dispatch_bwd_fast<B200RL_FP16>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, roll, g_num, g_den, st);
       default:
-        return dispatch_bwd_fast<B200RL_FP32>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, st);
+        return dispatch_bwd_fast<B200RL_FP32>(logits, ld, labels, lse, entropy, g_logp, g_ent, (int)T, (int)V, scale, inv_temp, dlogits, ld_out, roll, g_num, g_den, st);
     }
   }
   const unsigned grid = (unsigned)T;
@@ -622,17 +649,17 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
     case B200RL_BF16:
       logprob_bwd_plain_kernel<__nv_bfloat16><<<grid, kPlainThreads, 0, st>>>(
           (const __nv_bfloat16*)logits, ld, labels, lse, entropy, g_logp, g_ent, V, scale,
-          inv_temp, (__nv_bfloat16*)dlogits, ld_out);
+          inv_temp, (__nv_bfloat16*)dlogits, ld_out, roll, g_num, g_den);
       break;
     case B200RL_FP16:
       logprob_bwd_plain_kernel<__half><<<grid, kPlainThreads, 0, st>>>(
           (const __half*)logits, ld, labels, lse, entropy, g_logp, g_ent, V, scale, inv_temp,
-          (__half*)dlogits, ld_out);
+          (__half*)dlogits, ld_out, roll, g_num, g_den);
       break;
     case B200RL_FP32:
       logprob_bwd_plain_kernel<float><<<grid, kPlainThreads, 0, st>>>(
           (const float*)logits, ld, labels, lse, entropy, g_logp, g_ent, V, scale, inv_temp,
-          (float*)dlogits, ld_out);
+          (float*)dlogits, ld_out, roll, g_num, g_den);
       break;
     default:
       set_last_error("unsupported logits dtype code %d", dtype);
@@ -641,4 +668,4 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
   return check_launch("logprob_bwd_plain_kernel");
 }
 
-}  // extern "C"
+}  // namespace b200rl

@@ -39,19 +39,7 @@ LossWs loss_ws(void* ws, int64_t T) {
   return W;
 }
 
-struct Params {
-  const float *logp, *prox, *old, *adv;
-  const uint8_t* mask;
-  int64_t T;
-  float clip_lo, clip_hi, c_clip, cap;
-  const double *adv_mean, *adv_denom;
-  const int32_t* adv_group;
-  float* adv_out;
-  float *s_loss, *s_iw, *s_kl;
-  uint8_t *s_clip, *s_dual;
-  float *s_bw, *s_bkl;
-  uint8_t* s_bm;
-  float *dlogp, *loss, *denom;
+struct Params : PpoLossArgs {
   unsigned int* counter;
   double* partial;
 };
@@ -68,7 +56,7 @@ __global__ void __launch_bounds__(kThreads) ppo_loss_fwd_kernel(const Params p) 
     for (int k = 0; k < kPerThread; k++) {
       const int64_t t = base + k * kThreads + tid;
       if (t >= p.T) break;
-      const bool m = p.mask[t] != 0;
+      const bool m = p.mask ? p.mask[t] != 0 : p.mask_f32[t] != 0.f;
       const float lp = p.logp[t], px = p.prox[t], ol = p.old[t];
       float A = p.adv[t];
       if (norm) {
@@ -93,6 +81,11 @@ __global__ void __launch_bounds__(kThreads) ppo_loss_fwd_kernel(const Params p) 
       if (p.s_bkl) p.s_bkl[t] = tk.bkl;
       if (p.s_bm) p.s_bm[t] = tk.bmask;
       if (p.dlogp) p.dlogp[t] = tk.dlogp;
+      if (p.s_valid) p.s_valid[t] = m;
+      if (p.s_clip_ratio) p.s_clip_ratio[t] = tk.clip ? 1.f : 0.f;
+      if (p.s_dual_ratio) p.s_dual_ratio[t] = tk.dual ? 1.f : 0.f;
+      if (p.s_clip_new) p.s_clip_new[t] = tk.clip ? lp : 0.f;
+      if (p.s_clip_old) p.s_clip_old[t] = tk.clip ? ol : 0.f;
     }
   }
   // block reduce (fp64)
@@ -144,6 +137,30 @@ ppo_loss_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ g
 }
 
 }  // namespace
+
+int ppo_loss_fwd_launch(const PpoLossArgs& a, void* workspace, size_t workspace_bytes, void* stream) {
+  B200RL_REQUIRE(a.T >= 0, "negative T");
+  B200RL_REQUIRE(a.loss && a.denom && workspace, "loss/denom/workspace must not be null");
+  B200RL_REQUIRE(a.T == 0 || (a.logp && a.prox && a.old && a.adv && (a.mask || a.mask_f32)),
+                 "null input pointer");
+  B200RL_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "workspace must be 256-B aligned");
+  B200RL_REQUIRE(!(a.c_clip > 0.f) || a.c_clip > 1.f, "c_clip must be > 1 (functional.py:157), got %f",
+                 a.c_clip);
+  LossWs W = loss_ws(workspace, a.T);
+  if (workspace_bytes < W.bytes) {
+    set_last_error("ppo loss workspace too small: %zu < %zu", workspace_bytes, W.bytes);
+    return B200RL_EWORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200RL_CUDA(cudaMemsetAsync(workspace, 0, 256, st));
+  Params p;
+  static_cast<PpoLossArgs&>(p) = a;
+  p.counter = W.counter;
+  p.partial = W.partial;
+  ppo_loss_fwd_kernel<<<W.blocks, kThreads, 0, st>>>(p);
+  return check_launch("ppo_loss_fwd_kernel");
+}
+
 }  // namespace b200rl
 
 extern "C" {
@@ -162,20 +179,7 @@ int b200rl_ppo_loss_fwd(const float* logp, const float* prox_logp, const float* 
                         float* stat_behave_imp_weight, float* stat_behave_approx_kl,
                         uint8_t* stat_behave_mask, float* dlogp, float* loss, float* denom,
                         void* workspace, size_t workspace_bytes, void* stream) {
-  using namespace b200rl;
-  B200RL_REQUIRE(T >= 0, "negative T");
-  B200RL_REQUIRE(loss && denom && workspace, "loss/denom/workspace must not be null");
-  B200RL_REQUIRE(T == 0 || (logp && prox_logp && old_logp && adv && mask), "null input pointer");
-  B200RL_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "workspace must be 256-B aligned");
-  B200RL_REQUIRE(!(c_clip > 0.f) || c_clip > 1.f, "c_clip must be > 1 (functional.py:157), got %f", c_clip);
-  LossWs W = loss_ws(workspace, T);
-  if (workspace_bytes < W.bytes) {
-    set_last_error("ppo loss workspace too small: %zu < %zu", workspace_bytes, W.bytes);
-    return B200RL_EWORKSPACE;
-  }
-  cudaStream_t st = (cudaStream_t)stream;
-  B200RL_CUDA(cudaMemsetAsync(workspace, 0, 256, st));
-  Params p;
+  b200rl::PpoLossArgs p{};
   p.logp = logp; p.prox = prox_logp; p.old = old_logp; p.adv = adv; p.mask = mask; p.T = T;
   p.clip_lo = clip_lo; p.clip_hi = clip_hi; p.c_clip = c_clip; p.cap = cap;
   p.adv_mean = adv_mean; p.adv_denom = adv_denom; p.adv_group = adv_group; p.adv_out = adv_out;
@@ -183,9 +187,7 @@ int b200rl_ppo_loss_fwd(const float* logp, const float* prox_logp, const float* 
   p.s_clip = stat_clip_mask; p.s_dual = stat_dual_clip_mask;
   p.s_bw = stat_behave_imp_weight; p.s_bkl = stat_behave_approx_kl; p.s_bm = stat_behave_mask;
   p.dlogp = dlogp; p.loss = loss; p.denom = denom;
-  p.counter = W.counter; p.partial = W.partial;
-  ppo_loss_fwd_kernel<<<W.blocks, kThreads, 0, st>>>(p);
-  return check_launch("ppo_loss_fwd_kernel");
+  return b200rl::ppo_loss_fwd_launch(p, workspace, workspace_bytes, stream);
 }
 
 int b200rl_ppo_loss_bwd(const float* dlogp, const float* grad_loss, const float* denom,

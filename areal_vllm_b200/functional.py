@@ -125,14 +125,30 @@ def masked_normalization(
     for d in dims:
         group_elems *= x.shape[d]
     if xf.numel() == 0 or group_elems == 0:
+        # an empty shard still has to join the collective (the reference all-reduces zero moments,
+        # functional.py:108-115): the other ranks of reduce_group are waiting in it
+        if dist.is_initialized() and all_reduce:
+            G = 1
+            for d in keep:
+                G *= x.shape[d]
+            if G > 0:
+                dist.all_reduce(torch.zeros(G, 3, dtype=torch.float64, device=x.device),
+                                op=dist.ReduceOp.SUM, group=reduce_group)
         return x.float()
-    mom = ops.masked_moments(xf.view(-1), None if mf is None else mf.view(-1), group_elems, None, 1)
-    if dist.is_initialized() and all_reduce:
-        dist.all_reduce(mom, op=dist.ReduceOp.SUM, group=reduce_group)
-    mean, denom = ops.moments_finalize(mom, False, bool(unbiased), float(eps))
-    out = ops.masked_normalize(
-        xf.view(-1), None if mf is None else mf.view(-1), mean, group_elems, denom, group_elems, True
-    ).view(xf.shape)
+    reduce = dist.is_initialized() and all_reduce
+    if not reduce and not torch.compiler.is_compiling():
+        # no collective in the middle: moments -> finalize -> normalise in one host call
+        out = ops._raw_masked_normalize_groups(
+            xf.view(-1), None if mf is None else mf.view(-1), group_elems, bool(unbiased), float(eps)
+        ).view(xf.shape)
+    else:
+        mom = ops.masked_moments(xf.view(-1), None if mf is None else mf.view(-1), group_elems, None, 1)
+        if reduce:
+            dist.all_reduce(mom, op=dist.ReduceOp.SUM, group=reduce_group)
+        mean, denom = ops.moments_finalize(mom, False, bool(unbiased), float(eps))
+        out = ops.masked_normalize(
+            xf.view(-1), None if mf is None else mf.view(-1), mean, group_elems, denom, group_elems, True
+        ).view(xf.shape)
     if needs_perm:
         inv = [0] * nd
         for i, p in enumerate(perm):

@@ -16,6 +16,7 @@ from __future__ import annotations
 from typing import List, Optional, Tuple
 
 import ctypes
+from ctypes import c_void_p
 
 import torch
 
@@ -320,6 +321,128 @@ class _GrpoFusedFn(torch.autograd.Function):
         if g is None:
             return None, None, None, None
         return scale_inplace_(dlogits, g), None, None, None
+
+
+# --------------------------------------------------------------------------------------------
+# H2-d composite: grpo_loss_fn as two launches forward, one launch backward (eager only)
+# --------------------------------------------------------------------------------------------
+# rows of the fp32 slab / of the bool slab that one call of b200rl_grpo_loss_fwd fills
+GL_F32 = ("logp", "lse", "dlogp", "entropy", "rowmax", "rowmin", "s_loss", "s_iw", "s_kl", "s_bw", "s_bkl",
+          "clip_ratio", "dual_clip_ratio", "clipped_new_logp", "clipped_old_logp")
+GL_U8 = ("s_clip", "s_dual", "s_bm", "valid")
+_GL_CORE = 3  # without stats only logp, lse, dlogp exist
+
+
+def _tokvec(t: Tensor, T: int, name: str) -> Tensor:
+    if t.shape != (T,):
+        raise RuntimeError(f"{name} must have shape ({T},), got {tuple(t.shape)}")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be on CUDA (b200rl has no CPU path)")
+    if t.dtype != torch.float32:
+        t = t.to(torch.float32)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _raw_grpo_loss_fwd(logits: Tensor, input_ids: Tensor, roll: bool, prox_logp: Tensor, old_logp: Tensor,
+                       adv: Tensor, mask: Tensor, temperature: float, clip_lo: float, clip_hi: float,
+                       c_clip: float, cap: float, want_stats: bool):
+    """-> (scalars [2] fp32 = (loss, N), fp32 slab [15 or 3, Tp], bool slab [4, Tp] or None).
+    One host call, two launches; every output of the step lives in the two slabs (rows GL_F32 /
+    GL_U8, row stride Tp = T rounded up to 64) so the call allocates four tensors, not twenty."""
+    _check_logits(logits, input_ids)
+    T, V = logits.shape
+    dev = logits.device
+    px, ol, ad = _tokvec(prox_logp.detach(), T, "prox_logp"), _tokvec(old_logp.detach(), T, "logprobs"), \
+        _tokvec(adv.detach(), T, "advantages")
+    if mask.shape != (T,) or not mask.is_cuda:
+        raise RuntimeError(f"loss_mask must be a CUDA tensor of shape ({T},)")
+    if mask.dtype == torch.float32:
+        mk, mf = mask, 1
+    else:
+        mk, mf = (mask if mask.dtype == torch.bool else mask != 0), 0
+    if not mk.is_contiguous():
+        mk = mk.contiguous()
+    Tp = (T + 63) // 64 * 64
+    nf = len(GL_F32) if want_stats else _GL_CORE
+    fs = torch.empty((nf, Tp), dtype=torch.float32, device=dev)
+    bs = torch.empty((len(GL_U8), Tp), dtype=torch.bool, device=dev) if want_stats else None
+    sc = torch.empty(2, dtype=torch.float32, device=dev)
+    ws = torch.empty(max(lib.b200rl_grpo_loss_workspace_bytes(T), 256), dtype=torch.uint8, device=dev)
+    fb, st4 = fs.data_ptr(), Tp * 4
+    f = lambda i: c_void_p(fb + i * st4) if i < nf else None
+    bb = bs.data_ptr() if want_stats else 0
+    b = (lambda i: c_void_p(bb + i * Tp)) if want_stats else (lambda i: None)
+    sp = sc.data_ptr()
+    with _on(dev):
+        rc = lib.b200rl_grpo_loss_fwd(
+            ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
+            ptr(input_ids), int(roll), T, V, float(temperature), ptr(px), ptr(ol), ptr(ad), ptr(mk), mf,
+            float(clip_lo), float(clip_hi), float(c_clip), float(cap),
+            f(0), f(3), f(1), f(4), f(5),                      # logp, entropy, lse, rowmax, rowmin
+            f(6), f(7), f(8), b(0), b(1), f(9), f(10), b(2),   # the reference's eight stats
+            b(3), f(11), f(12), f(13), f(14),                  # valid, ratios, clipped logps
+            f(2), c_void_p(sp), c_void_p(sp + 4), ptr(ws), ws.numel(), stream_handle(dev))
+    check(rc, "b200rl_grpo_loss_fwd")
+    return sc, fs, bs
+
+
+class _GrpoLossFn(torch.autograd.Function):
+    """loss = grpo_loss_fn(logits, ...); backward = one launch producing dlogits."""
+
+    @staticmethod
+    def forward(ctx, logits, input_ids, roll, prox_logp, old_logp, adv, mask, temperature, clip_lo, clip_hi,
+                c_clip, cap, want_stats):
+        sc, fs, bs = _raw_grpo_loss_fwd(logits, input_ids, roll, prox_logp, old_logp, adv, mask, temperature,
+                                        clip_lo, clip_hi, c_clip, cap, want_stats)
+        ctx.save_for_backward(logits, input_ids, fs, sc)
+        ctx.roll, ctx.temperature = bool(roll), float(temperature)
+        ctx.set_materialize_grads(False)
+        loss = sc[0]
+        if bs is None:
+            ctx.mark_non_differentiable(fs)
+            return loss, fs
+        ctx.mark_non_differentiable(fs, bs)
+        return loss, fs, bs
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        if g_loss is None:
+            return (None,) * 13
+        logits, input_ids, fs, sc = ctx.saved_tensors
+        T, V = logits.shape
+        dev = logits.device
+        gl = g_loss if g_loss.dtype == torch.float32 else g_loss.to(torch.float32)
+        dlogits = torch.empty((T, V), dtype=logits.dtype, device=dev)
+        fb, st4, sp = fs.data_ptr(), fs.stride(0) * 4, sc.data_ptr()
+        with _on(dev):
+            rc = lib.b200rl_grpo_loss_bwd(
+                ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
+                ptr(input_ids), int(ctx.roll), T, V, ctx.temperature, c_void_p(fb + st4), c_void_p(fb + 2 * st4),
+                ptr(gl), c_void_p(sp + 4), ptr(dlogits), V, stream_handle(dev))
+        check(rc, "b200rl_grpo_loss_bwd")
+        return (dlogits,) + (None,) * 12
+
+
+def grpo_loss(logits, input_ids, roll, prox_logp, old_logp, adv, mask, temperature, clip_lo, clip_hi, c_clip,
+              cap, want_stats):
+    """-> (loss, {name: [T] view}) ; eager mode only (the caller keeps the custom-op path for compiled
+    graphs). The dict has the GL_F32 / GL_U8 rows (three of them without stats)."""
+    if logits.requires_grad and torch.is_grad_enabled():
+        out = _GrpoLossFn.apply(logits, input_ids, roll, prox_logp, old_logp, adv, mask, temperature, clip_lo,
+                                clip_hi, c_clip, cap, want_stats)
+        loss, fs, bs = out if want_stats else (out[0], out[1], None)
+    else:
+        sc, fs, bs = _raw_grpo_loss_fwd(logits, input_ids, roll, prox_logp, old_logp, adv, mask, temperature,
+                                        clip_lo, clip_hi, c_clip, cap, want_stats)
+        loss = sc[0]
+    T = logits.shape[0]
+    if fs.shape[1] != T:
+        fs = fs[:, :T]
+        bs = None if bs is None else bs[:, :T]
+    rows = dict(zip(GL_F32, fs.unbind(0)))
+    if bs is not None:
+        rows.update(zip(GL_U8, bs.unbind(0)))
+    return loss, rows
 
 
 # --------------------------------------------------------------------------------------------
@@ -820,6 +943,28 @@ def masked_normalize(x, mask, mean, mean_group_elems, denom, denom_group_elems, 
     if _eager():
         return _raw_masked_normalize(x, mask, mean, mean_group_elems, denom, denom_group_elems, mask_x)
     return masked_normalize_op(x, mask, mean, mean_group_elems, denom, denom_group_elems, mask_x)
+
+
+def _raw_masked_normalize_groups(x: Tensor, mask: Optional[Tensor], group_elems: int, unbiased: bool,
+                                 eps: float) -> Tensor:
+    """(x*mask - mean[g]) / (std[g] + eps) per group of `group_elems` consecutive elements, same
+    level for mean and std, no collective: one host call (three launches). x, mask flat fp32."""
+    _lib.require_cuda(x=x, mask=mask)
+    _lib.require_contiguous(x=x, mask=mask)
+    n, dev = x.numel(), x.device
+    out = torch.empty_like(x, dtype=torch.float32)
+    if n == 0:
+        return out
+    G = n // group_elems
+    st = torch.empty((G, 5), dtype=torch.float64, device=dev)  # moments [G,3] | mean [G] | denom [G]
+    ws = torch.empty(max(lib.b200rl_moments_workspace_bytes(n, group_elems), 256), dtype=torch.uint8, device=dev)
+    sb = st.data_ptr()
+    with _on(dev):
+        rc = lib.b200rl_masked_normalize_groups(
+            ptr(x), ptr(mask), n, group_elems, int(unbiased), float(eps), ptr(out), c_void_p(sb),
+            c_void_p(sb + G * 24), c_void_p(sb + G * 32), ptr(ws), ws.numel(), stream_handle(dev))
+    check(rc, "b200rl_masked_normalize_groups")
+    return out
 
 
 # --------------------------------------------------------------------------------------------

@@ -8,7 +8,9 @@
  *
  * The library never allocates device memory: the caller owns every buffer,
  * including the scratch ("workspace") buffers whose size the *_workspace_bytes
- * helpers report. Nothing here synchronises the host with the device.
+ * helpers report. (One entry point, b200rl_gae_1d_nolp_misalign_noalloc, takes no
+ * workspace and uses a fixed scratch array built into the library image instead.)
+ * Nothing here synchronises the host with the device.
  *
  * Citations `ref:` are relative to the AReaL-vllm reference tree and name the
  * reference interface that each entry point replaces.
@@ -60,6 +62,48 @@ int b200rl_logprob_entropy_bwd(const void* logits, int dtype, int64_t ld, const 
                                const float* lse, const float* entropy, const float* g_logp,
                                const float* g_ent, int64_t T, int64_t V, float temperature,
                                void* dlogits, int64_t ld_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * H2-d  the actor step's loss function as the engine calls it, and its backward.
+ * ref: areal/engine/ppo/actor.py:292-367 (grpo_loss_fn) and loss.backward()
+ *      (areal/engine/fsdp_engine.py:542-550).
+ *
+ * fwd = b200rl_logprob_entropy_fwd followed by b200rl_ppo_loss_fwd on the fresh log-probs: two
+ *       launches and nothing between them.
+ *       - `input_ids` with label_roll != 0: the label of row t is input_ids[(t+1) % T], i.e.
+ *         torch.roll(input_ids, -1) (actor.py:308) evaluated as an index; label_roll == 0: the
+ *         array already holds the labels.
+ *       - `mask`: bytes (torch.bool) when mask_is_f32 == 0, else fp32 with non-zero = valid (the
+ *         engine's loss_mask is a float tensor that grpo_loss_fn turns into bool, actor.py:304).
+ *       - besides everything the two separate entry points write, the derived tensors that
+ *         grpo_loss_fn logs (actor.py:339-365): stat_valid (the mask as bytes), stat_clip_ratio /
+ *         stat_dual_clip_ratio (the two masks as fp32), stat_clipped_new_logp / _old_logp
+ *         (where(clip_mask, logp | old_logp, 0)). Every stat_* pointer, entropy, rowmax and rowmin
+ *         may be NULL; logp, lse, dlogp, loss, denom are required (the backward reads them).
+ * bwd = ONE launch: dlogits[t, :] = d(grad_loss * loss)/d logits with entropy detached
+ *       (actor.py:312): b200rl_ppo_loss_bwd's g_logp[t] = dlogp[t] * (grad_loss[0] / denom[0]) is
+ *       evaluated per row inside the log-prob backward kernel (same operation order, same bits as
+ *       the two separate calls). grad_loss and denom are DEVICE scalars.
+ * workspace: b200rl_grpo_loss_workspace_bytes(T) (= the PPO loss's), cleared by the call.
+ */
+size_t b200rl_grpo_loss_workspace_bytes(int64_t T);
+int b200rl_grpo_loss_fwd(const void* logits, int dtype, int64_t ld, const int64_t* input_ids,
+                         int label_roll, int64_t T, int64_t V, float temperature,
+                         const float* prox_logp, const float* old_logp, const float* adv,
+                         const void* mask, int mask_is_f32, float clip_lo, float clip_hi,
+                         float c_clip, float cap, float* logp, float* entropy, float* lse,
+                         float* rowmax, float* rowmin, float* stat_loss, float* stat_imp_weight,
+                         float* stat_approx_kl, uint8_t* stat_clip_mask,
+                         uint8_t* stat_dual_clip_mask, float* stat_behave_imp_weight,
+                         float* stat_behave_approx_kl, uint8_t* stat_behave_mask,
+                         uint8_t* stat_valid, float* stat_clip_ratio, float* stat_dual_clip_ratio,
+                         float* stat_clipped_new_logp, float* stat_clipped_old_logp, float* dlogp,
+                         float* loss, float* denom, void* workspace, size_t workspace_bytes,
+                         void* stream);
+int b200rl_grpo_loss_bwd(const void* logits, int dtype, int64_t ld, const int64_t* input_ids,
+                         int label_roll, int64_t T, int64_t V, float temperature, const float* lse,
+                         const float* dlogp, const float* grad_loss, const float* denom,
+                         void* dlogits, int64_t ld_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * H1 over a vocabulary-parallel (tensor-parallel) shard of the logits.
@@ -286,6 +330,15 @@ int b200rl_moments_finalize(const double* moments, int64_t n_groups, int centere
 int b200rl_masked_normalize(const float* x, const float* mask, int64_t n_elems,
                             const double* mean, int64_t mean_group_elems, const double* denom,
                             int64_t denom_group_elems, int mask_x, float* out, void* stream);
+/* The three calls above back to back for the common case of one process and the same level for
+ * mean and std (masked_normalization with all_reduce off, AdvNorm "group"/"group"):
+ * moments (raw second moment) -> finalize -> out = (x*mask - mean[g]) / denom[g], g = i / group_elems.
+ * `moments` [G,3], `mean` [G], `denom` [G] are caller-owned fp64 outputs. One host call, three
+ * launches; same bits as the separate calls. */
+int b200rl_masked_normalize_groups(const float* x, const float* mask, int64_t n_elems,
+                                   int64_t group_elems, int unbiased, double eps, float* out,
+                                   double* moments, double* mean, double* denom, void* workspace,
+                                   size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * H4  interval gather / scatter on a flat parameter buffer.

@@ -60,9 +60,9 @@ def run(dev, rank, world, scale=0.5, iters=4):
 
     def bcast(buf):
         if host_bcast:  # gloo: stage through the host (two ranks on one GPU; timing is not the point)
-            h = buf.view(torch.int16).cpu()
+            h = buf.view(torch.uint8).cpu()  # gloo moves bytes, not int16/bf16
             dist.broadcast(h, src=0)
-            buf.view(torch.int16).copy_(h)
+            buf.view(torch.uint8).copy_(h)
         else:
             dist.broadcast(buf, src=0)
 

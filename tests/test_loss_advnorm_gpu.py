@@ -300,3 +300,45 @@ def test_sharded_group_advantage_norm_matches_advnorm(world, cuda):
                 torch.testing.assert_close(out, full[idx[r]], rtol=1e-5, atol=1e-5)
             else:
                 assert out.shape == (0, L)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("T,V,mask_kind,want", [(300, 4096, "float", True), (64, 4100, "bool", True),
+                                                (1, 512, "float", True), (257, 151936, "bool", False),
+                                                (130, 1003, "int", True)])
+def test_grpo_loss_fast_path_equals_op_path(T, V, mask_kind, want, dtype, cuda):
+    """The two-launch composite (label roll as an index, fp32/bool mask read as is, logging tensors
+    written by the loss kernel, loss backward folded into the log-prob backward) against the
+    custom-op path it replaces in eager mode: same loss bits, same dlogits bits, same stats."""
+    from areal_vllm_b200 import actor
+
+    gen = torch.Generator().manual_seed(T + V)
+    logits = (torch.randn(T, V, generator=gen) * 2).to(dtype).to(cuda)
+    m = torch.rand(T, generator=gen) < 0.7
+    mask = {"float": m.float(), "bool": m, "int": m.long() * 3}[mask_kind]
+    data = {k: v.to(cuda) for k, v in dict(
+        input_ids=torch.randint(0, V, (T,), generator=gen), logprobs=-torch.rand(T, generator=gen) * 4,
+        advantages=torch.randn(T, generator=gen), loss_mask=mask, prox_logp=-torch.rand(T, generator=gen) * 4).items()}
+    scale = torch.tensor(0.37, device=cuda)
+    res = {}
+    for fast in (True, False):
+        actor.FAST_PATH = fast
+        try:
+            x = logits.clone().requires_grad_(True)
+            st = {} if want else None
+            loss = actor.grpo_loss_fn(x, data, 0.8, 0.2, 0.28, 3.0, 5.0, stats=st)
+            (loss * scale).backward()
+            with torch.no_grad():
+                loss_ng = actor.grpo_loss_fn(x.detach(), data, 0.8, 0.2, 0.28, 3.0, 5.0)
+            res[fast] = (loss.detach().clone(), x.grad.clone(), st, loss_ng.clone())
+        finally:
+            actor.FAST_PATH = True
+    (la, ga, sa, na), (lb, gb, sb, nb) = res[True], res[False]
+    assert torch.equal(la, lb) and torch.equal(na, nb) and torch.equal(la, na)
+    assert torch.equal(ga.view(torch.int16 if dtype != torch.float32 else torch.int32),
+                       gb.view(torch.int16 if dtype != torch.float32 else torch.int32))
+    if want:
+        assert set(sa) == set(sb)
+        for k in sa:
+            assert sa[k].dtype == sb[k].dtype and sa[k].shape == sb[k].shape, k
+            assert torch.equal(sa[k], sb[k]), k
