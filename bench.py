@@ -541,7 +541,7 @@ def run_cfg4(dev, rank, world, steps=2, check=True):
             lp.retain_grad()
             loss, _ = Fn.ppo_actor_loss_fn(lp, prox_lp[a:b], old_lp[a:b], adv[a:b], CLIP[0], mask[a:b],
                                            CLIP[1], CLIP[2], CLIP[3])
-            w = mask[a:b].sum() / total_w.float()
+            w = (mask[a:b].sum() / total_w.float()).reshape(())
             (loss * w).backward()
             scaled_loss += (loss.detach() * w).double()
             logp_l.append(lp.detach())
