@@ -29,11 +29,52 @@ namespace b200rl {
 namespace {
 
 // ============================ SERIAL =========================================
+// The kernel is ISSUE-bound (ncu, round 1: 4.1 warp instructions per token, issue slots 64 % busy,
+// DRAM 33 %): what it costs is instructions, not bytes. Round 2 therefore (i) anchors every
+// 256-token block at its TOP, so the block maps 1:1 onto the shared-memory slots, the chain always
+// starts on a 16-byte boundary and only the block that reaches the sequence's start is ragged;
+// (ii) addresses the block through three per-lane base pointers with compile-time offsets and takes
+// an unpredicated path for full blocks (the round-1 code spent ~1.4 instructions per token on 64-bit
+// index arithmetic and predicates); (iii) runs the chain 32 tokens per iteration: 32 dependent FMAs
+// + 8 LDS.128 + 8 STS.128, i.e. 1.5 instructions per token plus ~0.1 of loop overhead.
 constexpr int kSerWarps = 4;
-constexpr int kSerPerLane = 8;               // tokens per lane per block
+#ifndef B200RL_SER_PERLANE
+#define B200RL_SER_PERLANE 8
+#endif
+constexpr int kSerPerLane = B200RL_SER_PERLANE;  // tokens per lane per block
 constexpr int kSerBlk = 32 * kSerPerLane;    // 256 tokens per warp iteration: the 4-cycle/token
                                              // chain of one block (~1000 cycles) covers the DRAM
                                              // latency of the next block's prefetch
+
+struct SerBlock {
+  float r[kSerPerLane], v[kSerPerLane], vn[kSerPerLane];
+};
+
+// tokens [hi - 256, hi) of one sequence; slot j = 32*k + lane <-> token hi - 256 + j. Slots of
+// tokens below 0 (only in the block that reaches the sequence's start) are not loaded.
+__device__ __forceinline__ void ser_load(SerBlock& B, const float* __restrict__ rbase,
+                                         const float* __restrict__ vbase, int hi, int lane) {
+  const int lo = hi - kSerBlk;
+  const float* rp = rbase + lo + lane;
+  const float* vp = vbase + lo + lane;
+  if (lo >= 0) {  // warp-uniform: the common, unpredicated path
+#pragma unroll
+    for (int k = 0; k < kSerPerLane; k++) {
+      B.r[k] = __ldg(rp + 32 * k);
+      B.v[k] = __ldg(vp + 32 * k);
+      B.vn[k] = __ldg(vp + 32 * k + 1);
+    }
+  } else {
+    const int first = -lo - lane;  // slot 32*k + lane holds a token iff 32*k >= first
+#pragma unroll
+    for (int k = 0; k < kSerPerLane; k++) {
+      const bool ok = 32 * k >= first;
+      B.r[k] = ok ? __ldg(rp + 32 * k) : 0.f;
+      B.v[k] = ok ? __ldg(vp + 32 * k) : 0.f;
+      B.vn[k] = ok ? __ldg(vp + 32 * k + 1) : 0.f;
+    }
+  }
+}
 
 __global__ void __launch_bounds__(kSerWarps * 32)
 gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
@@ -49,105 +90,87 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
     const int rs = cu[i], re = cu[i + 1];
     const int n = re - rs;
     if (n <= 0) continue;
-    const int64_t vs = (int64_t)rs + i;
+    const float* rbase = rewards + rs;
+    const float* vbase = values + ((int64_t)rs + i);  // sequence i's values start at cu[i] + i
     const bool bs = boot[i] != 0;
     float X = 0.f;  // lastgae
-    // software prefetch of the first block
-    float r[kSerPerLane], v[kSerPerLane], vn[kSerPerLane];
+    SerBlock B;
     int hi = n;
-    int lo = max(hi - kSerBlk, 0);
-#pragma unroll
-    for (int k = 0; k < kSerPerLane; k++) {
-      int u = lo + 32 * k + lane;
-      bool ok = u < hi;
-      r[k] = ok ? rewards[rs + u] : 0.f;
-      v[k] = ok ? values[vs + u] : 0.f;
-      vn[k] = ok ? values[vs + u + 1] : 0.f;
-    }
+    ser_load(B, rbase, vbase, hi, lane);
+    // the sequence's last step without bootstrap sees next value 0 (gae.cu:20-21): slot 255 of
+    // the top block
+    if (!bs && lane == 31) B.vn[kSerPerLane - 1] = 0.f;
     while (hi > 0) {
-      const int cnt = hi - lo;
+      const int lo = hi - kSerBlk;
+      const int skip = lo < 0 ? -lo : 0;  // slots below `skip` hold no token
       // delta in the reference's contraction: fma(gamma, next_v, r) - v   (gae.cu:22-23)
       float vk[kSerPerLane];
 #pragma unroll
       for (int k = 0; k < kSerPerLane; k++) {
-        int u = lo + 32 * k + lane;
-        float nv = (u == n - 1 && !bs) ? 0.f : vn[k];
-        float dl = __fsub_rn(__fmaf_rn(gamma, nv, r[k]), v[k]);
-        if (u < hi) d[32 * k + lane] = dl;
-        vk[k] = v[k];
+        d[32 * k + lane] = __fsub_rn(__fmaf_rn(gamma, B.vn[k], B.r[k]), B.v[k]);
+        vk[k] = B.v[k];
       }
-      // prefetch next block (to the left) while the chain runs
-      const int nhi = lo, nlo = max(lo - kSerBlk, 0);
-#pragma unroll
-      for (int k = 0; k < kSerPerLane; k++) {
-        int u = nlo + 32 * k + lane;
-        bool ok = u < nhi;
-        r[k] = ok ? rewards[rs + u] : 0.f;
-        v[k] = ok ? values[vs + u] : 0.f;
-        vn[k] = ok ? values[vs + u + 1] : 0.f;
-      }
+      // prefetch the next block (to the left) while the chain runs
+      if (lo > 0) ser_load(B, rbase, vbase, lo, lane);
       __syncwarp();
       if (lane == 0) {
-        int q = cnt - 1;
-        // ragged top down to a multiple of 8, then 8 tokens per step with two 16-B smem loads that
-        // are issued one step (8 dependent FMAs = 32 cycles) ahead, which covers the ~29-cycle
-        // shared-memory latency: only the FMA chain is on the critical path
-        for (; (q & 7) != 7 && q >= 0; q--) {
+        int q = kSerBlk - 1;
+        // 32 tokens per iteration: eight 16-byte loads up front (the first FMA needs only the first
+        // of them), 32 dependent FMAs in the reference's order, eight 16-byte stores
+#pragma unroll 1
+        for (; q - 31 >= skip; q -= 32) {
+          float4 t[8];
+#pragma unroll
+          for (int g = 0; g < 8; g++) t[g] = *reinterpret_cast<const float4*>(d + q - 3 - 4 * g);
+#pragma unroll
+          for (int g = 0; g < 8; g++) {
+            t[g].w = X = __fmaf_rn(c, X, t[g].w);
+            t[g].z = X = __fmaf_rn(c, X, t[g].z);
+            t[g].y = X = __fmaf_rn(c, X, t[g].y);
+            t[g].x = X = __fmaf_rn(c, X, t[g].x);
+          }
+#pragma unroll
+          for (int g = 0; g < 8; g++) *reinterpret_cast<float4*>(d + q - 3 - 4 * g) = t[g];
+        }
+#pragma unroll 1
+        for (; q - 3 >= skip; q -= 4) {
+          float4 t = *reinterpret_cast<const float4*>(d + q - 3);
+          t.w = X = __fmaf_rn(c, X, t.w);
+          t.z = X = __fmaf_rn(c, X, t.z);
+          t.y = X = __fmaf_rn(c, X, t.y);
+          t.x = X = __fmaf_rn(c, X, t.x);
+          *reinterpret_cast<float4*>(d + q - 3) = t;
+        }
+#pragma unroll 1
+        for (; q >= skip; q--) {
           X = __fmaf_rn(c, X, d[q]);
           d[q] = X;
-        }
-        if (q >= 7) {
-          // two register sets in ping-pong (no copies between them): while one set runs its 8
-          // dependent FMAs the other one's two 16-byte loads are in flight
-          auto chain8 = [&](float4& h4, float4& l4, float* at) {
-            h4.w = X = __fmaf_rn(c, X, h4.w);
-            h4.z = X = __fmaf_rn(c, X, h4.z);
-            h4.y = X = __fmaf_rn(c, X, h4.y);
-            h4.x = X = __fmaf_rn(c, X, h4.x);
-            l4.w = X = __fmaf_rn(c, X, l4.w);
-            l4.z = X = __fmaf_rn(c, X, l4.z);
-            l4.y = X = __fmaf_rn(c, X, l4.y);
-            l4.x = X = __fmaf_rn(c, X, l4.x);
-            *reinterpret_cast<float4*>(at - 3) = h4;
-            *reinterpret_cast<float4*>(at - 7) = l4;
-          };
-          float4 ah = *reinterpret_cast<float4*>(d + q - 3);
-          float4 al = *reinterpret_cast<float4*>(d + q - 7);
-          float4 bh = make_float4(0.f, 0.f, 0.f, 0.f), bl = bh;
-          while (true) {
-            const bool more1 = q >= 15;
-            if (more1) {
-              bh = *reinterpret_cast<float4*>(d + q - 11);
-              bl = *reinterpret_cast<float4*>(d + q - 15);
-            }
-            chain8(ah, al, d + q);
-            q -= 8;
-            if (!more1) break;
-            const bool more2 = q >= 15;
-            if (more2) {
-              ah = *reinterpret_cast<float4*>(d + q - 11);
-              al = *reinterpret_cast<float4*>(d + q - 15);
-            }
-            chain8(bh, bl, d + q);
-            q -= 8;
-            if (!more2) break;
-          }
         }
       }
       __syncwarp();
       X = __shfl_sync(0xffffffffu, X, 0);
+      float* ap = adv + rs + lo + lane;
+      float* tp = ret + rs + lo + lane;
+      if (lo >= 0) {
 #pragma unroll
-      for (int k = 0; k < kSerPerLane; k++) {
-        int u = lo + 32 * k + lane;
-        if (u < hi) {
-          float A = d[32 * k + lane];
-          adv[rs + u] = A;
-          ret[rs + u] = __fadd_rn(A, vk[k]);  // gae.cu:26
+        for (int k = 0; k < kSerPerLane; k++) {
+          const float A = d[32 * k + lane];
+          ap[32 * k] = A;
+          tp[32 * k] = __fadd_rn(A, vk[k]);  // gae.cu:26
+        }
+      } else {
+        const int first = skip - lane;
+#pragma unroll
+        for (int k = 0; k < kSerPerLane; k++) {
+          if (32 * k >= first) {
+            const float A = d[32 * k + lane];
+            ap[32 * k] = A;
+            tp[32 * k] = __fadd_rn(A, vk[k]);
+          }
         }
       }
       __syncwarp();
-      hi = nhi;
-      lo = nlo;
+      hi = lo;
     }
   }
 }
@@ -305,6 +328,240 @@ int launch_serial_batched(const float* rewards, const float* values, const int32
   if (grid > cap) grid = cap;
   k<<<grid, kBatWarps * 32, smem, st>>>(rewards, values, cu, boot, adv, ret, batch, gamma, lam);
   return check_launch("gae_serial_batched_kernel");
+}
+
+// ============================ SERIAL, slots ==================================
+// What limits gae_serial_kernel is not arithmetic or issue slots but the shared-memory pipe (ncu,
+// round 2: mio_throttle 4.0 + short_scoreboard 4.4 stalled warps per issue, issue slots 45 % busy):
+// its chain lane moves every token through shared memory with single-lane 16-byte accesses, and
+// a one-lane LDS.128/STS.128 occupies the pipe like a full-warp one. Here a warp owns EIGHT
+// sequence "slots" and lane s < 8 runs the chain of slot s, so one LDS.128/FFMA/STS.128 warp
+// instruction serves eight chains (the pipe cost per token drops 8x). Unlike
+// gae_serial_batched_kernel, slots are independent: each walks its own sequence from the top in
+// 64-token blocks and takes the next unprocessed sequence (a global ticket counter) as soon as its
+// own ends, so unequal lengths cost nothing (the batched kernel waits for the longest of its 8).
+// Raw rewards/values of the NEXT block of all 8 slots are staged by 4-byte cp.async (any
+// alignment, coalesced per slot) into the other half of a 2-stage ring while the chains run; the
+// chain lane computes delta itself - fma(gamma, v_next, r) - v, then fma(c, X, delta), the
+// reference's order and contractions, so the result is bit-identical - and overwrites r with adv
+// and v with ret in place; all 32 lanes then write the rows out coalesced.
+#ifndef B200RL_SLOTS_MIN_BATCH
+#define B200RL_SLOTS_MIN_BATCH 49152
+#endif
+constexpr int kSlots = 8;            // sequences in flight per warp
+#ifndef B200RL_SLOT_BLK
+#define B200RL_SLOT_BLK 64
+#endif
+constexpr int kSlotBlk = B200RL_SLOT_BLK;  // tokens per slot per round (32 or 64)
+constexpr int kSlotPitch = kSlotBlk + 4;   // floats per row: the tokens + the block's next value, padded so
+                                     // that the 8 chain lanes' 16-byte accesses hit distinct banks
+constexpr int kSlotWarps = 4;
+constexpr int kSlotStage = 2 * kSlots * kSlotPitch;  // floats per stage: R rows then V rows
+struct __align__(16) SlotDesc {
+  int rpos, vpos;  // global index of row slot 0 in rewards (= adv/ret) and in values
+  int skip;        // row slots < skip hold no token (kSlotBlk = the slot is idle)
+  int flags;       // bit 0: the block is its sequence's top; bit 1: that sequence bootstraps
+};
+#ifndef B200RL_SLOT_STAGES
+#define B200RL_SLOT_STAGES 2
+#endif
+constexpr int kSlotStages = B200RL_SLOT_STAGES;  // ring depth: blocks staged ahead of the chains
+constexpr size_t kSlotWarpBytes = kSlotStages * (kSlotStage * sizeof(float) + kSlots * sizeof(SlotDesc));
+constexpr size_t kSlotSmem = (size_t)kSlotWarps * kSlotWarpBytes;
+
+__device__ __forceinline__ void cp_async4_s(uint32_t smem_dst, const float* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+
+__global__ void __launch_bounds__(kSlotWarps * 32)
+gae_serial_slots_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+                        const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot,
+                        float* __restrict__ adv, float* __restrict__ ret, int batch, float gamma,
+                        float lam, unsigned int* __restrict__ ticket) {
+  extern __shared__ __align__(16) unsigned char slot_smem[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float* ring = reinterpret_cast<float*>(slot_smem + (size_t)w * kSlotWarpBytes);
+  SlotDesc* dsc = reinterpret_cast<SlotDesc*>(ring + kSlotStages * kSlotStage);  // [kSlotStages][kSlots]
+  const float c = __fmul_rn(gamma, lam);  // ref gae.cu:24
+  const bool chain_lane = lane < kSlots;
+
+  // ---- per-slot state, held by lane s < 8 ------------------------------------------------------
+  int hi = 0, rs = 0, vs = 0, n = 0;      // current sequence: tokens [0, hi) still to do
+  bool bflag = false;
+  int nx_i = batch, nx_rs = 0, nx_re = 0;  // the sequence after it, fetched one sequence ahead
+  bool nx_boot = false;
+  // without a ticket counter: static round-robin over all slots of the grid
+  int static_next = (blockIdx.x * kSlotWarps + w) * kSlots + lane;
+  const int static_stride = gridDim.x * kSlotWarps * kSlots;
+  auto fetch_next = [&]() {
+    int i;
+    if (ticket) {
+      i = (int)atomicAdd(ticket, 1u);
+    } else {
+      i = static_next;
+      static_next += static_stride;
+    }
+    if (i < 0 || i >= batch) i = batch;
+    nx_i = i;
+    if (i < batch) {
+      nx_rs = cu[i];
+      nx_re = cu[i + 1];
+      nx_boot = boot[i] != 0;
+    }
+  };
+  auto refill = [&]() {  // rare: once per sequence
+    while (nx_i < batch && nx_re - nx_rs <= 0) fetch_next();  // empty sequences produce nothing
+    if (nx_i >= batch) return;
+    rs = nx_rs;
+    n = nx_re - nx_rs;
+    vs = nx_rs + nx_i;  // values of sequence i start at cu[i] + i
+    bflag = nx_boot;
+    hi = n;
+    fetch_next();
+  };
+  auto next_desc = [&]() {
+    SlotDesc D{0, 0, kSlotBlk, 0};
+    if (!chain_lane) return D;
+    if (hi <= 0) refill();
+    if (hi <= 0) return D;
+    const int lo = hi - kSlotBlk;
+    D.skip = lo < 0 ? -lo : 0;
+    D.rpos = rs + lo;
+    D.vpos = vs + lo;
+    D.flags = (hi == n ? 1 : 0) | (bflag ? 2 : 0);
+    hi = lo > 0 ? lo : 0;
+    return D;
+  };
+  // all 32 lanes: stage the blocks described by dsc[stage] into ring[stage]. Branch-free: the
+  // eight descriptors are loaded first (one 16-byte broadcast load each, all in flight together),
+  // every copy is predicated on its row slot holding a token (idle slots have skip = kSlotBlk).
+  auto issue = [&](int stage) {
+    const uint32_t sR = smem_u32(ring + stage * kSlotStage) + lane * 4;
+    const uint32_t sV = sR + kSlots * kSlotPitch * 4;
+    const SlotDesc* D = dsc + stage * kSlots;
+    SlotDesc d[kSlots];
+#pragma unroll
+    for (int q = 0; q < kSlots; q++) d[q] = D[q];
+#pragma unroll
+    for (int q = 0; q < kSlots; q++) {
+      const float* rp = rewards + d[q].rpos + lane;
+      const float* vp = values + d[q].vpos + lane;
+      const uint32_t r0 = sR + q * kSlotPitch * 4, v0 = sV + q * kSlotPitch * 4;
+      if (lane >= d[q].skip) {
+        cp_async4_s(r0, rp);
+        cp_async4_s(v0, vp);
+      }
+      if (kSlotBlk > 32 && lane + 32 >= d[q].skip) {
+        cp_async4_s(r0 + 128, rp + 32);
+        cp_async4_s(v0 + 128, vp + 32);
+      }
+      // the value after the block's top token
+      if (lane == 0 && d[q].skip < kSlotBlk) cp_async4_s(v0 + kSlotBlk * 4, vp + kSlotBlk);
+    }
+  };
+
+  if (chain_lane) fetch_next();
+  // prologue: kSlotStages - 1 blocks per slot in flight
+#pragma unroll
+  for (int p = 0; p < kSlotStages - 1; p++) {
+    const SlotDesc d0 = next_desc();
+    if (chain_lane) dsc[p * kSlots + lane] = d0;
+    __syncwarp();
+    issue(p);
+    cp_async_commit();
+  }
+  float X = 0.f;  // lastgae of this lane's slot
+  int stage = 0;
+  for (;;) {
+    const SlotDesc cur = dsc[stage * kSlots + (lane & (kSlots - 1))];
+    if (!__any_sync(0xffffffffu, chain_lane && cur.skip < kSlotBlk)) break;  // every slot has run dry
+    const int fill = stage == 0 ? kSlotStages - 1 : stage - 1;  // the stage freed by the previous round
+    const SlotDesc nxt = next_desc();
+    if (chain_lane) dsc[fill * kSlots + lane] = nxt;
+    __syncwarp();
+    issue(fill);
+    cp_async_commit();
+    cp_async_wait<kSlotStages - 1>();
+    __syncwarp();
+    float* R = ring + stage * kSlotStage;
+    float* V = R + kSlots * kSlotPitch;
+    // ---- 8 chains, one per lane, 4 tokens per step, in the reference's order --------------------
+    if (chain_lane && cur.skip < kSlotBlk) {
+      float* rrow = R + lane * kSlotPitch;
+      const float* vrow = V + lane * kSlotPitch;
+      if (cur.flags & 1) X = 0.f;
+      float nv = vrow[kSlotBlk];
+      if ((cur.flags & 3) == 1) nv = 0.f;  // gae.cu:20-21: the last step without bootstrap
+      const int gmin = cur.skip >> 2;      // groups below hold no token (the lowest may be partial:
+                                           // its empty slots are computed on stale data and never
+                                           // written out, and the sequence ends there)
+      // two register sets in ping-pong (no copies between them): while one group's four
+      // dependent FMAs run, the other group's two 16-byte loads are in flight
+      auto step4 = [&](const float4& r4, const float4& v4, float* at) {
+        float4 a4;
+        a4.w = X = __fmaf_rn(c, X, __fsub_rn(__fmaf_rn(gamma, nv, r4.w), v4.w));    // gae.cu:22-24
+        a4.z = X = __fmaf_rn(c, X, __fsub_rn(__fmaf_rn(gamma, v4.w, r4.z), v4.z));
+        a4.y = X = __fmaf_rn(c, X, __fsub_rn(__fmaf_rn(gamma, v4.z, r4.y), v4.y));
+        a4.x = X = __fmaf_rn(c, X, __fsub_rn(__fmaf_rn(gamma, v4.y, r4.x), v4.x));
+        nv = v4.x;
+        *reinterpret_cast<float4*>(at) = a4;  // adv over the rewards; the values stay
+      };
+      int g = kSlotBlk / 4 - 1;
+      float4 ra = *reinterpret_cast<const float4*>(rrow + 4 * g);
+      float4 va = *reinterpret_cast<const float4*>(vrow + 4 * g);
+      float4 rb = ra, vb = va;
+#pragma unroll 1
+      while (true) {
+        const bool more1 = g - 1 >= gmin;
+        if (more1) {
+          rb = *reinterpret_cast<const float4*>(rrow + 4 * g - 4);
+          vb = *reinterpret_cast<const float4*>(vrow + 4 * g - 4);
+        }
+        step4(ra, va, rrow + 4 * g);
+        if (!more1) break;
+        const bool more2 = g - 2 >= gmin;
+        if (more2) {
+          ra = *reinterpret_cast<const float4*>(rrow + 4 * g - 8);
+          va = *reinterpret_cast<const float4*>(vrow + 4 * g - 8);
+        }
+        step4(rb, vb, rrow + 4 * g - 4);
+        if (!more2) break;
+        g -= 2;
+      }
+    }
+    __syncwarp();
+    // ---- rows out, coalesced; ret = adv + v (gae.cu:26) by all lanes; branch-free like issue() ----
+    {
+      const float* Rl = R + lane;
+      const float* Vl = V + lane;
+      const SlotDesc* D = dsc + stage * kSlots;
+      SlotDesc d[kSlots];
+#pragma unroll
+      for (int q = 0; q < kSlots; q++) d[q] = D[q];
+#pragma unroll
+      for (int q = 0; q < kSlots; q++) {
+        float* ap = adv + d[q].rpos + lane;
+        float* tp = ret + d[q].rpos + lane;
+        const float a0 = Rl[q * kSlotPitch];
+        const float t0 = __fadd_rn(a0, Vl[q * kSlotPitch]);
+        if (lane >= d[q].skip) {
+          ap[0] = a0;
+          tp[0] = t0;
+        }
+        if (kSlotBlk > 32) {
+          const float a1 = Rl[q * kSlotPitch + 32];
+          const float t1 = __fadd_rn(a1, Vl[q * kSlotPitch + 32]);
+          if (lane + 32 >= d[q].skip) {
+            ap[32] = a1;
+            tp[32] = t1;
+          }
+        }
+      }
+    }
+    __syncwarp();  // the stage (and its descriptors) are rewritten by the next round
+    stage = stage + 1 == kSlotStages ? 0 : stage + 1;
+  }
+  cp_async_wait<0>();
 }
 
 // ============================ SCAN ===========================================
@@ -981,14 +1238,43 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
     const float c = gamma * lam;
     mode = (c > 0.99f || !(c >= 0.f)) ? B200RL_GAE_SERIAL : B200RL_GAE_SCAN;
   }
-  // Many SHORT sequences (< 64 tokens on average): one chain per lane beats one warp per sequence
-  // (measured, 500k sequences of 1-64 tokens: 144 us vs 291 us; 65,536: 29 us vs 44 us). For longer
-  // sequences the per-row staging overhead loses to the warp kernel, so those stay there.
+  // SERIAL picks among four kernels that produce the same bits (measured on B200,
+  // scripts/time_gae_modes.py, 2026-11 build):
+  //   slots   8 independent chains per warp with ticket refill: wins once there are enough sequences
+  //           to keep ~28k slots busy - >= 32k short sequences (500k x [1,64]: 84 us vs 144 us for
+  //           the 32-per-warp kernel, 216 us for warp-per-sequence), >= 48k longer ones (65,536 x
+  //           [64,2048]: 361 us vs 387 us; 131,072: 675 us vs 762 us);
+  //   batch8  8 sequences per warp in lock step: 16k-32k short sequences (< 64 tokens on average);
+  //   warp    one warp per sequence: everything else (few or long sequences).
   const bool short_seqs = total < (int64_t)batch * 64;
-  if (mode == B200RL_GAE_SERIAL_BATCH32 || (mode == B200RL_GAE_SERIAL && short_seqs && batch >= 131072))
+  const bool use_slots = mode == B200RL_GAE_SERIAL_SLOTS ||
+                         (mode == B200RL_GAE_SERIAL && batch >= (short_seqs ? 32768 : B200RL_SLOTS_MIN_BATCH));
+  if (mode == B200RL_GAE_SERIAL_BATCH32)
     return launch_serial_batched<32, 32, 2>(rewards, values, cu_seqlens, bootstrap, adv, ret, batch, gamma, lam, st);
-  if (mode == B200RL_GAE_SERIAL_BATCH8 || (mode == B200RL_GAE_SERIAL && short_seqs && batch >= 16384))
+  if (mode == B200RL_GAE_SERIAL_BATCH8 || (mode == B200RL_GAE_SERIAL && !use_slots && short_seqs && batch >= 16384))
     return launch_serial_batched<8, 128, 2>(rewards, values, cu_seqlens, bootstrap, adv, ret, batch, gamma, lam, st);
+  if (use_slots) {
+    static bool slot_attr[64] = {false};
+    int dev = 0;
+    B200RL_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !slot_attr[dev]) {
+      B200RL_CUDA(cudaFuncSetAttribute(gae_serial_slots_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kSlotSmem));
+      slot_attr[dev] = true;
+    }
+    unsigned int* ticket = nullptr;  // with a workspace: sequences are handed out by a ticket counter
+    if (workspace && workspace_bytes >= sizeof(unsigned int) &&
+        (reinterpret_cast<uintptr_t>(workspace) & 3) == 0) {
+      ticket = static_cast<unsigned int*>(workspace);
+      B200RL_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st));
+    }
+    int grid = (batch + kSlotWarps * kSlots - 1) / (kSlotWarps * kSlots);
+    const int cap = sm_count() * (int)(220 * 1024 / (kSlotSmem + 1024));
+    if (grid > cap) grid = cap;
+    gae_serial_slots_kernel<<<grid, kSlotWarps * 32, kSlotSmem, st>>>(
+        rewards, values, cu_seqlens, bootstrap, adv, ret, batch, gamma, lam, ticket);
+    return check_launch("gae_serial_slots_kernel");
+  }
   if (mode == B200RL_GAE_SERIAL || mode == B200RL_GAE_SERIAL_WARP) {
     int grid = (batch + kSerWarps - 1) / kSerWarps;
     const int cap = sm_count() * 16;

@@ -23,8 +23,8 @@ __all__ = [
 ]
 
 _MODES = {"auto": _lib.GAE_AUTO, "serial": _lib.GAE_SERIAL, "scan": _lib.GAE_SCAN,
-          # SERIAL chooses among these three by batch size (identical bits); forcing is for tests
-          "serial_warp": 3, "serial_batch8": 4, "serial_batch32": 5}
+          # SERIAL chooses among these four by batch size (identical bits); forcing is for tests
+          "serial_warp": 3, "serial_batch8": 4, "serial_batch32": 5, "serial_slots": 6}
 
 
 def gae_1d_nolp_misalign(

@@ -361,6 +361,36 @@ def run_extras(dev, peak, compiled_baseline=False):
         torch.cuda.empty_cache()
     except Exception as e:  # an OOM or similar here must not cost the headline line
         out["torch_gpu_path"] = {"error": repr(e)[:200]}
+    # The two other ways the reference enters H1: forward only, once per batch, for
+    # the proximal log-probs (`calc_logprobs`, areal/engine/ppo/actor.py:55-58: 2*V B/token), and
+    # fp32 logits as the Megatron engine hands them over (megatron_engine.py:510-521: 4*V forward,
+    # 8*V backward). Same T as a cfg2 micro-batch; the inputs are far larger than L2.
+    try:
+        Th = 10240
+        gen = torch.Generator(device=dev).manual_seed(12)
+        variants = []
+        for dt, esz in ((torch.bfloat16, 2), (torch.float32, 4)):
+            xh = torch.empty(Th, V, dtype=dt, device=dev)
+            for lo_ in range(0, Th, 2048):
+                xh[lo_:lo_ + 2048] = (torch.randn(2048, V, generator=gen, device=dev) * 2).to(dt)
+            yh = torch.randint(0, V, (Th,), generator=gen, device=dev)
+            gl = torch.randn(Th, generator=gen, device=dev)
+            ms_f = timeit(lambda: pkg.functional.gather_logprobs(xh, yh, TEMPERATURE), iters=10)
+            ms_fe = timeit(lambda: pkg.functional.gather_logprobs_entropy(xh, yh, TEMPERATURE), iters=10)
+            _, _, lse_h, _, _ = pkg.ops.logprob_entropy_fwd(xh, yh, TEMPERATURE, False, False)
+            ms_b = timeit(lambda: pkg.ops.logprob_entropy_bwd(xh, yh, lse_h, lse_h, gl, None, TEMPERATURE), iters=10)
+            for what, ms_, nbytes in (("forward only: gather_logprobs (compute_logp)", ms_f, esz * V),
+                                      ("forward: gather_logprobs_entropy", ms_fe, esz * V),
+                                      ("backward: dlogits", ms_b, 2 * esz * V)):
+                gbps = nbytes * Th / (ms_ * 1e-3) / 1e9
+                variants.append({"logits": str(dt).replace("torch.", ""), "call": what, "tokens": Th, "us": ms_ * 1e3,
+                                 "tokens_per_s": Th / (ms_ * 1e-3), "algorithmic_bytes_per_token": nbytes,
+                                 "GBps": gbps, "frac_of_measured_peak": gbps / peak})
+            del xh
+            torch.cuda.empty_cache()
+        out["h1_call_site_variants"] = variants
+    except Exception as e:
+        out["h1_call_site_variants"] = {"error": repr(e)[:200]}
     for name, B, lo, hi, seed in (("cfg1: 256 seqs, len 64-2048", 256, 64, 2048, 1),
                                   ("cfg1 length law x256: 65536 seqs", 65536, 64, 2048, 2)):
         rng = np.random.default_rng(seed)
@@ -374,7 +404,8 @@ def run_extras(dev, peak, compiled_baseline=False):
         for gamma, lam in ((0.99, 0.95), (1.0, 1.0)):
             ms = timeit(lambda: pkg.ppo_functional.cugae1d_nolp_misalign_func(r, v, cu, b, gamma, lam))
             rec = {"workload": name, "gamma": gamma, "lam": lam, "tokens": total,
-                   "kernel": "gae_pieces_kernel (tiled scan)" if gamma * lam <= 0.99 else "gae_serial_kernel",
+                   "kernel": "gae_pieces_kernel (tiled scan)" if gamma * lam <= 0.99 else
+                   ("gae_serial_slots_kernel" if B >= 49152 else "gae_serial_kernel"),
                    "us": ms * 1e3, "tokens_per_s": total / (ms * 1e-3),
                    "hbm_frac_of_measured_peak": 16.0 * total / (ms * 1e-3) / 1e9 / peak}
             if B == 256:  # CPU baseline: C port of pygae1d_nolp_misalign, one thread (the python
@@ -418,6 +449,25 @@ def run_extras(dev, peak, compiled_baseline=False):
             "set_GBps": gb / (ms_t * 1e-3), "set_frac_of_measured_peak": gb / (ms_t * 1e-3) / peak, **rec_move})
         del src, packed
     return out
+
+def roofline_gae(extras, peak, peak_src):
+    """BASELINE.json's metric is "...; GAE tokens/s": the GAE kernels' own roofline entries (16
+    algorithmic bytes per token: r, v in; adv, ret out), one per (gamma, lam) of configs[0], at the
+    size where a roofline means something (65,536 sequences of the cfg1 length law, 1.1 GB) and
+    at cfg1 itself (256 sequences = 4.4 MB: launch-latency bound), with the CPU baseline beside it."""
+    if not extras or not extras.get("gae"):
+        return None
+    out = []
+    for g in extras["gae"]:
+        gbps = 16.0 * g["tokens"] / (g["us"] * 1e-6) / 1e9
+        out.append({"kernel": g["kernel"], "workload": g["workload"], "gamma": g["gamma"], "lam": g["lam"],
+                    "bound": "hbm", "achieved": gbps, "peak": peak, "unit": "GB/s", "frac": gbps / peak,
+                    "peak_source": peak_src, "algorithmic_bytes_per_token": 16, "tokens_per_s": g["tokens_per_s"],
+                    "cpu_baseline_tokens_per_s": g.get("cpu_port_tokens_per_s"),
+                    "cpu_baseline_kind": "port (C restatement of pygae1d_nolp_misalign, 1 thread)"
+                    if "cpu_port_tokens_per_s" in g else None})
+    return out
+
 
 # ------------------------------------------------------------------------------------------
 # BASELINE config 4 (long-CoT, strong scaling): 1,048,576 tokens of 1k-16k-token sequences, whole
@@ -975,7 +1025,8 @@ def main_b200rl(args):
                        "cache": f"inputs larger than L2: {N_LOGITS_BUFFERS} rotating logits buffers of "
                                 f"{max_T}x{V} bf16 = {max_T * V * 2 / 1e9:.2f} GB each"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "clocks": clocks,
-            "fused_step": fused, "strong_scaling": cfg4, "parity": parity, "extra": extras,
+            "fused_step": fused, "strong_scaling": cfg4, "parity": parity,
+            "roofline_gae": roofline_gae(extras, peak, peak_src), "extra": extras,
             "gpu_launches": args.steps * (3 + 3 * n_mb),
             "gpu_launches_note": "per step: masked_moments+moments_finalize+masked_normalize, then per "
                                  "micro-batch logprob_fwd, ppo_loss_fwd, logprob_bwd (the scalar loss's "

@@ -182,7 +182,7 @@ def test_padded_gae_golden(cuda):
         np.testing.assert_allclose(out.cpu().numpy(), g[f"adv_{k}"], rtol=1e-5, atol=1e-5)
 
 
-@pytest.mark.parametrize("mode", ["serial_batch8", "serial_batch32"])
+@pytest.mark.parametrize("mode", ["serial_batch8", "serial_batch32", "serial_slots"])
 @pytest.mark.parametrize("B,lo,hi", [(1, 1, 5), (7, 1, 300), (33, 64, 2048), (1000, 1, 130), (4099, 0, 70)])
 @pytest.mark.parametrize("gl", [(1.0, 1.0), (0.99, 0.95)])
 def test_batched_serial_kernels_bit_identical(mode, B, lo, hi, gl, cuda):
@@ -208,6 +208,30 @@ def test_batched_serial_kernels_bit_identical(mode, B, lo, hi, gl, cuda):
     assert np.array_equal(a.cpu().numpy(), a_ref) and np.array_equal(t.cpu().numpy(), t_ref)
     a2, t2 = PF.gae_1d_nolp_misalign(to(r), to(v), to(cu), to(boot), *gl, mode="serial_warp")
     assert torch.equal(a, a2) and torch.equal(t, t2)
+
+
+@pytest.mark.parametrize("B,lo,hi", [(3, 1, 200), (300, 0, 700), (9000, 30, 400)])
+def test_slots_kernel_without_ticket_counter(B, lo, hi, cuda):
+    """B200RL_GAE_SERIAL_SLOTS called through the C ABI with NO workspace (static round-robin over
+    the slots instead of the ticket counter): same bits as the one-warp-per-sequence kernel."""
+    from areal_vllm_b200 import _lib
+    from areal_vllm_b200 import ppo_functional as PF
+
+    rng = np.random.default_rng(B)
+    lens = rng.integers(lo, hi + 1, B)
+    lens[0] = max(lens[0], 1)
+    total = int(lens.sum())
+    to = lambda a: torch.from_numpy(a).to(cuda)
+    r, v = to(rng.standard_normal(total).astype(np.float32)), to(rng.standard_normal(total + B).astype(np.float32))
+    cu = to(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32))
+    boot = to(rng.random(B) < 0.5)
+    adv, ret = torch.full_like(r, 7.0), torch.full_like(r, 7.0)
+    rc = _lib.lib.b200rl_gae_1d_nolp_misalign(_lib.ptr(r), _lib.ptr(v), _lib.ptr(cu), _lib.ptr(boot.view(torch.uint8)),
+                                              _lib.ptr(adv), _lib.ptr(ret), B, total, 1.0, 1.0, 6, None, 0,
+                                              _lib.stream_handle(cuda))
+    assert rc == 0, _lib.last_error()
+    a2, t2 = PF.gae_1d_nolp_misalign(r, v, cu, boot, 1.0, 1.0, mode="serial_warp")
+    assert torch.equal(adv, a2) and torch.equal(ret, t2)
 
 
 def test_serial_auto_dispatch_large_batch(cuda):

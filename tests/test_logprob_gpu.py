@@ -220,3 +220,57 @@ def test_full_size_cfg3_properties(cuda):
     assert float(rs.abs().max()) < 2e-2 * float(g_lp.abs().max())
     lp_sub, ent_sub = BF.gather_logprobs_entropy(x.detach()[pick].contiguous(), labels[pick], 0.7)
     assert torch.equal(lp_sub, lp.detach()[pick]) and torch.equal(ent_sub, ent.detach()[pick])
+
+
+@pytest.mark.parametrize("temp", [1.0, 0.7])
+def test_full_size_cfg3_loss_args_and_entropy_bonus(temp, cuda):
+    """BASELINE config 3 at full size with ITS loss arguments (decoupled weights on,
+    eps_clip 0.2 / eps_clip_higher 0.28, c_clip 3.0, cap 5.0) and the non-zero g_H variant
+    (entropy bonus 0.01*mean(H) added to the loss, so the backward takes the HAS_GH kernel with a
+    different upstream per row): loss, per-token stats and dlogits of a row subset against the
+    oracle's eager fp32 torch path run on those rows on the GPU."""
+    from areal_vllm_b200 import functional as BF
+    from oracle import torch_ref
+
+    T, V = 32768, 152064
+    free, _ = torch.cuda.mem_get_info()
+    if free < 26 * 2**30:
+        pytest.skip("needs ~21 GB of free HBM")
+    gen = torch.Generator(device=cuda).manual_seed(33)
+    x = torch.empty(T, V, dtype=torch.bfloat16, device=cuda)
+    for lo in range(0, T, 4096):
+        x[lo:lo + 4096] = (torch.randn(4096, V, generator=gen, device=cuda) * 2).bfloat16()
+    ids = torch.randint(0, V, (T,), generator=gen, device=cuda)
+    labels = torch.roll(ids, -1)
+    rows = torch.arange(0, T, 2, device=cuda)
+    x[rows, labels[rows]] += 6.0
+    mask = torch.rand(T, generator=gen, device=cuda) < 0.8
+    adv = torch.randn(T, generator=gen, device=cuda)
+    args = dict(eps_clip=0.2, eps_clip_higher=0.28, c_clip=3.0, behav_imp_weight_cap=5.0)
+
+    xg = x.requires_grad_(True)
+    lp, ent = BF.gather_logprobs_entropy(xg, labels, temp)
+    old = lp.detach() + 0.3 * torch.randn(T, generator=gen, device=cuda)   # wide enough to hit both clips
+    prox = lp.detach() + 0.2 * torch.randn(T, generator=gen, device=cuda)
+    loss, stat = BF.ppo_actor_loss_fn(lp, prox, old, adv, loss_mask=mask, **args)
+    total = loss - 0.01 * ent.mean()
+    total.backward()
+    assert int(stat["clip_mask"].sum()) > 100 and int(stat["dual_clip_mask"].sum()) > 10
+
+    # the same computation with the oracle on a row subset; N and T enter through the constants
+    pick = torch.randperm(T, generator=gen, device=cuda)[:128].sort().values
+    xs = x.detach()[pick].clone().requires_grad_(True)
+    lp_r, ent_r = torch_ref.logprobs_entropy(xs, labels[pick], temp)
+    _close(lp[pick], lp_r.detach().cpu().numpy())
+    _close(ent[pick], ent_r.detach().cpu().numpy())
+    # per-token loss terms of the subset (mask-count independent), then the full-batch scaling
+    loss_r, stat_r = torch_ref.ppo_actor_loss(lp_r, prox[pick], old[pick], adv[pick], 0.2, mask[pick], 0.28, 3.0, 5.0)
+    n_all, n_sub = int(mask.sum()), max(int(mask[pick].sum()), 1)
+    (loss_r * (n_sub / n_all) - 0.01 * ent_r.sum() / T).backward()
+    for k in ("loss", "importance_weight", "approx_kl", "behave_imp_weight", "behave_approx_kl"):
+        _close(stat[k][pick], stat_r[k].detach().cpu().numpy())
+    for k in ("clip_mask", "dual_clip_mask", "behave_mask"):
+        assert torch.equal(stat[k][pick], stat_r[k])
+    _close(xg.grad[pick], xs.grad.float().cpu().numpy(), rtol=G_RTOL, atol=1e-9)
+    # whole-batch loss from the per-token stats (fp64 on the host side of the check)
+    np.testing.assert_allclose(loss.item(), float((stat["loss"].double() * mask).sum() / n_all), rtol=1e-5)
