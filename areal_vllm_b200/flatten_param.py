@@ -47,18 +47,26 @@ def clear_plan_cache() -> None:
 
 
 def _plan(intervals: torch.Tensor, packed_numel: int, elem_size: int, big_numel: int):
+    """-> (workspace, reuse, key). A miss hands out a fresh workspace that is NOT yet in the cache:
+    the caller registers it with ``_remember`` only after the op that builds the plan has returned
+    without raising, so a failed call (strided tensor, misaligned pointer, launch error) can never
+    leave an uninitialised plan behind for the next call to reuse."""
     key = (intervals.data_ptr(), intervals._version, intervals.shape[0], packed_numel, elem_size,
            big_numel, intervals.device.index)
     hit = _PLAN_CACHE.get(key)
     if hit is not None:
         _PLAN_CACHE.move_to_end(key)
-        return hit[0], True
+        return hit[0], True, key
     nbytes = _lib.lib.b200rl_interval_workspace_bytes(intervals.shape[0], packed_numel, elem_size)
-    ws = _lib.workspace(nbytes, intervals.device)
-    _PLAN_CACHE[key] = (ws, intervals)  # keep the intervals alive so the pointer stays unique
+    return _lib.workspace(nbytes, intervals.device), False, key
+
+
+def _remember(key, ws: torch.Tensor, keep_alive) -> None:
+    """Cache a plan that a successful call has just built (``keep_alive``: the intervals tensors,
+    so that their data pointers stay unique while the entry lives)."""
+    _PLAN_CACHE[key] = (ws, keep_alive)
     while len(_PLAN_CACHE) > _PLAN_CACHE_MAX:
         _PLAN_CACHE.popitem(last=False)
-    return ws, False
 
 
 def _to_cuda_intervals(intervals_cpu, device) -> torch.Tensor:
@@ -70,8 +78,13 @@ def _slice_impl(src: torch.Tensor, intervals: torch.Tensor, total_size: int) -> 
     ops._check_intervals(intervals)
     if intervals.shape[0] == 0 or total_size == 0:
         return torch.empty((total_size,), dtype=src.dtype, device=src.device)
-    ws, reuse = _plan(intervals, total_size, src.element_size(), src.numel())
-    return ops.slice_intervals_op(src, intervals, int(total_size), ws, reuse)
+    _lib.require_cuda(src=src)
+    _lib.require_contiguous(src=src)  # all host-side validation before a plan is built or reused
+    ws, reuse, key = _plan(intervals, total_size, src.element_size(), src.numel())
+    out = ops.slice_intervals_op(src, intervals, int(total_size), ws, reuse)
+    if not reuse:
+        _remember(key, ws, intervals)
+    return out
 
 
 def _set_impl(src: torch.Tensor, dst: torch.Tensor, intervals: torch.Tensor) -> None:
@@ -80,8 +93,12 @@ def _set_impl(src: torch.Tensor, dst: torch.Tensor, intervals: torch.Tensor) -> 
         raise RuntimeError("Source and destination tensors must have the same dtype")
     if intervals.shape[0] == 0 or src.numel() == 0:
         return None
-    ws, reuse = _plan(intervals, src.numel(), src.element_size(), dst.numel())
+    _lib.require_cuda(src=src, dst=dst)
+    _lib.require_contiguous(src=src, dst=dst)
+    ws, reuse, key = _plan(intervals, src.numel(), src.element_size(), dst.numel())
     ops.set_intervals_op(src, dst, intervals, ws, reuse)
+    if not reuse:
+        _remember(key, ws, intervals)
     return None
 
 
@@ -215,8 +232,7 @@ def move_intervals(
         nbytes = _lib.lib.b200rl_move_workspace_bytes(src_intervals_cuda.shape[0], dst_intervals_cuda.shape[0],
                                                       total_size, es)
         ws, reuse = _lib.workspace(nbytes, dst.device), False
-        _PLAN_CACHE[key] = (ws, (src_intervals_cuda, dst_intervals_cuda))
-        while len(_PLAN_CACHE) > _PLAN_CACHE_MAX:
-            _PLAN_CACHE.popitem(last=False)
     ops.move_intervals_raw(src, dst, src_intervals_cuda, dst_intervals_cuda, total_size, ws, reuse)
+    if not reuse:  # only a plan that a successful call has built may be reused
+        _remember(key, ws, (src_intervals_cuda, dst_intervals_cuda))
     return None

@@ -313,6 +313,7 @@ class _GrpoFusedFn(torch.autograd.Function):
     def forward(ctx, logits, loss_unscaled, dlogits, upstream):
         ctx.save_for_backward(dlogits)
         ctx.set_materialize_grads(False)
+        ctx.consumed = False
         return loss_unscaled * upstream.reshape(()) if upstream is not None else loss_unscaled.clone()
 
     @staticmethod
@@ -320,6 +321,14 @@ class _GrpoFusedFn(torch.autograd.Function):
         (dlogits,) = ctx.saved_tensors
         if g is None:
             return None, None, None, None
+        if ctx.consumed:
+            # the stored gradient is handed out (and rescaled) IN PLACE; a second pass through this
+            # node would scale it again and may alias what the first pass returned as logits.grad
+            raise RuntimeError(
+                "the fused GRPO step's gradient was already consumed by a previous backward(); "
+                "retain_graph / a second backward through this node is not supported - use "
+                "grpo_loss_fn (the two-kernel path) for that")
+        ctx.consumed = True
         return scale_inplace_(dlogits, g), None, None, None
 
 

@@ -8,6 +8,7 @@ csrc/cugae/gae.cu:30-60 (gae_1d_nolp_misalign).
 
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -22,6 +23,8 @@ __all__ = [
     "actor_loss_fn",
 ]
 
+_VALIDATE_DEFAULT = os.environ.get("B200RL_VALIDATE", "0") not in ("", "0")
+
 _MODES = {"auto": _lib.GAE_AUTO, "serial": _lib.GAE_SERIAL, "scan": _lib.GAE_SCAN,
           # SERIAL chooses among these four by batch size (identical bits); forcing is for tests
           "serial_warp": 3, "serial_batch8": 4, "serial_batch32": 5, "serial_slots": 6}
@@ -35,11 +38,27 @@ def gae_1d_nolp_misalign(
     gamma: float,
     lmbda: float,
     mode: str = "auto",
+    validate: Optional[bool] = None,
 ) -> List[torch.Tensor]:
     """The pybind entry ``realhf._C.cugae.gae_1d_nolp_misalign`` (gae.cu:30-60): same argument
     checks (device, contiguity, shapes, dtypes) raising RuntimeError, returns ``[adv, ret]``.
-    The reference's two ``.item()`` checks on cu_seqlens (gae.cu:48-49) are host syncs and are
-    not repeated here. ``mode``: "auto" | "serial" | "scan" (see include/b200rl.h)."""
+    ``mode``: "auto" | "serial" | "scan" (see include/b200rl.h).
+
+    The reference also checks ``cu_seqlens[0] == 0`` and ``cu_seqlens[-1] == total`` (gae.cu:48-49)
+    with two ``.item()`` calls, i.e. two device->host syncs per call, and zero-fills its outputs.
+    By default neither happens here (the step must not sync; the kernels overwrite every token of a
+    well-formed ``cu_seqlens``), so a MALFORMED ``cu_seqlens`` is undefined behaviour: tokens
+    outside ``[cu[0], cu[-1])`` stay uninitialised and ``cu[-1] > total`` reads/writes out of
+    bounds. Pass ``validate=True`` (or set ``B200RL_VALIDATE=1``) to get the reference's check and
+    its RuntimeError at the price of one sync - e.g. while bringing up a new data pipeline."""
+    if validate is None:
+        validate = _VALIDATE_DEFAULT
+    if validate and cu_seqlens.numel() >= 1 and cu_seqlens.is_cuda:
+        first, last = (int(x) for x in cu_seqlens[[0, -1]].tolist())  # one sync
+        if first != 0 or last != rewards.shape[0]:
+            raise RuntimeError(
+                f"cu_seqlens must start at 0 and end at the total sequence length "
+                f"({rewards.shape[0]}), got [{first}, ..., {last}]")
     adv, ret = ops.gae_1d_nolp_misalign(
         rewards, values, cu_seqlens, bootstrap, float(gamma), float(lmbda), _MODES[mode]
     )

@@ -110,6 +110,42 @@ def fill_logits(buf: torch.Tensor, labels_even_peak: torch.Tensor, seed: int):
 
 
 # ------------------------------------------------------------------------------------------
+# host placement: run each rank on the CPUs of its GPU's NUMA node, so that the pinned staging
+# buffers of the e2e leg are first-touched there and the H2D copies do not cross the socket link
+# ------------------------------------------------------------------------------------------
+def bind_to_gpu_numa(local: int):
+    """-> {"numa_node": n, "cpus": count, "bdf": "..."}; never raises (a box without the sysfs
+    entries, or a single-node box, just reports what it found)."""
+    info = {"numa_node": None, "cpus": None, "bdf": None}
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        bdf = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bdf = bdf.decode() if isinstance(bdf, bytes) else bdf
+        bdf = bdf.lower()
+        if len(bdf.split(":")[0]) == 8:  # nvml prints an 8-digit domain, sysfs a 4-digit one
+            bdf = bdf[4:]
+        info["bdf"] = bdf
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+        if node < 0:
+            return info
+        info["numa_node"] = node
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info["cpus"] = len(cpus)
+    except Exception as e:
+        info["error"] = repr(e)[:120]
+    return info
+
+
+# ------------------------------------------------------------------------------------------
 # clocks sampling (B200_PROFILING.md)
 # ------------------------------------------------------------------------------------------
 class ClockSampler:
@@ -686,6 +722,7 @@ def main_b200rl(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    numa = bind_to_gpu_numa(local) if world > 1 else {"numa_node": None, "note": "single rank: not bound"}
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -929,14 +966,21 @@ def main_b200rl(args):
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
+        my_gbps = h2d_bytes * n_e2e / (ms * 1e-3) / 1e9
+        per_rank = [{"rank": rank, "h2d_GBps": my_gbps, **numa}]
         if world > 1:
             t = torch.tensor([ms], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
+            box = [None] * world
+            dist.all_gather_object(box, per_rank[0])
+            per_rank = box
         e2e = {"value": total_tok * n_e2e / (ms * 1e-3), "unit": "tokens/s",
                "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4, "steps": n_e2e,
-               "note": "logits+labels+per-token inputs start in pinned host memory; H2D double-buffered "
-                       "on a copy stream; loss read back each step"}
+               "per_rank": per_rank,
+               "note": "logits+labels+per-token inputs start in pinned host memory (each rank bound to the "
+                       "CPUs of its GPU's NUMA node before pinning); H2D double-buffered on a copy stream; "
+                       "loss read back each step; h2d_bytes_per_step is per rank"}
         del pin_logits, stage
 
     cpu_baseline = None

@@ -162,3 +162,19 @@ def test_fused_full_size_cfg2_microbatch(cuda):
     assert float(gb[pick].float().sum(-1).abs().max()) < 2e-2 * float(g_lp.abs().max())  # bf16 rounding only
     (lp_r * g_lp[pick]).sum().backward()
     np.testing.assert_allclose(gb[pick].float().cpu().numpy(), xs.grad.float().cpu().numpy(), rtol=8e-3, atol=1e-9)
+
+
+def test_fused_second_backward_is_refused(cuda):
+    """The fused node hands out (and rescales) its stored gradient in place, so a second pass
+    through it would scale twice: it must raise instead of returning silently wrong gradients."""
+    from areal_vllm_b200.actor import grpo_loss_fn_fused
+
+    logits, data = _batch(64, 4096, 9)
+    dd = {k: v.to(cuda) for k, v in data.items()}
+    xg = logits.to(cuda).requires_grad_(True)
+    loss = grpo_loss_fn_fused(xg, dd, 1.0, 0.2, None, None, 5.0)
+    (loss * 2.0).backward(retain_graph=True)
+    first = xg.grad.clone()
+    with pytest.raises(RuntimeError, match="already consumed"):
+        (loss * 2.0).backward()
+    assert torch.equal(xg.grad, first)

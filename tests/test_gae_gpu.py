@@ -275,3 +275,18 @@ def test_cfg4_full(gl, cuda):
     a_cuda, r_cuda = cpu_ref.gae_cuda_order(r, v, cu, b, *gl)
     adv, ret = _run((r, v, cu, b, *gl), cuda, "serial")
     assert np.array_equal(adv, a_cuda) and np.array_equal(ret, r_cuda)
+
+
+def test_validate_flag_reproduces_the_reference_check(cuda):
+    """gae.cu:48-49 / ppo_functional.py:365: cu_seqlens must start at 0 and end at total. Off by
+    default (it costs a host sync); validate=True raises the RuntimeError the reference raises."""
+    from areal_vllm_b200 import ppo_functional as PF
+
+    r = torch.randn(10, device=cuda)
+    v = torch.randn(12, device=cuda)
+    b = torch.ones(2, dtype=torch.bool, device=cuda)
+    good = torch.tensor([0, 4, 10], dtype=torch.int32, device=cuda)
+    PF.gae_1d_nolp_misalign(r, v, good, b, 0.9, 0.9, validate=True)
+    for bad in ([1, 4, 10], [0, 4, 9]):
+        with pytest.raises(RuntimeError, match="cu_seqlens must start at 0"):
+            PF.gae_1d_nolp_misalign(r, v, torch.tensor(bad, dtype=torch.int32, device=cuda), b, 0.9, 0.9, validate=True)

@@ -212,3 +212,40 @@ def test_cfg5_full_size(cuda):
         want = rows[permc[4 * lo: 4 * (lo + 5000)], :h].reshape(-1, 4 * h)
         assert torch.equal(got[lo:lo + 5000, : 4 * h], want)
     assert int(got[:, 4 * h:].abs().max()) == 0
+
+
+def test_failed_call_leaves_no_plan_behind(cuda):
+    """A call that raises after the plan workspace was handed out (here: a strided source) must
+    not leave that uninitialised workspace in the plan cache: the corrected call with the SAME
+    intervals tensor has to build the plan and give the right bytes (flatten_param)."""
+    from areal_vllm_b200 import flatten_param as FP
+
+    FP.clear_plan_cache()
+    rng = np.random.default_rng(77)
+    size, n = 200_003, 900
+    s_ = size // n
+    iv = np.array([(i * s_ + (i % 5), i * s_ + (i % 5) + 30 + (i % 11)) for i in range(n)], dtype=np.int64)
+    rng.shuffle(iv)
+    ivc = torch.from_numpy(iv).to(cuda)
+    total = int((iv[:, 1] - iv[:, 0]).sum())
+    big = torch.from_numpy(rng.integers(-32768, 32767, 2 * size, dtype=np.int16)).to(cuda).view(torch.bfloat16)
+    strided = big[::2]
+    with pytest.raises(RuntimeError):
+        FP.slice_intervals(strided, intervals_cuda=ivc, output_size=total)
+    assert len(FP._PLAN_CACHE) == 0
+    good = strided.contiguous()
+    out = FP.slice_intervals(good, intervals_cuda=ivc, output_size=total)
+    ref = torch.cat([good[a:b] for a, b in iv.tolist()])
+    assert torch.equal(out.view(torch.int16), ref.view(torch.int16))
+    # same for set: strided destination first, then the real one
+    dst = torch.zeros(2 * size, dtype=torch.bfloat16, device=cuda)
+    with pytest.raises(RuntimeError):
+        FP.set_intervals(out, dst[::2], intervals_cuda=ivc)
+    d2 = torch.zeros(size, dtype=torch.bfloat16, device=cuda)
+    FP.set_intervals(out, d2, intervals_cuda=ivc)
+    chk = torch.zeros(size, dtype=torch.bfloat16, device=cuda)
+    off = 0
+    for a, b in iv.tolist():
+        chk[a:b] = out[off:off + b - a]
+        off += b - a
+    assert torch.equal(d2.view(torch.int16), chk.view(torch.int16))

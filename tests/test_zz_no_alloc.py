@@ -93,3 +93,38 @@ def test_no_alloc_rejects_oversize(cuda):
     tail = adv[-4:].cpu().numpy()
     np.testing.assert_allclose(tail, [0.125, 0.25, 0.5, 1.0], rtol=1e-6)
     assert float(adv[0]) == 0.0
+
+
+def test_no_alloc_takes_no_device_memory_and_any_stream(cuda):
+    """torch's own counters only see torch's caching allocator; a cudaMalloc inside the library
+    would slip past them. So the driver's free-memory figure is compared across warmed-up calls
+    (pre-allocated outputs, synchronised on both sides), on the current stream and on a side stream."""
+    from areal_vllm_b200 import _lib
+
+    r, v, cu, b, B, total = _case(200, 50, 3000, 23, cuda)
+    a_ws, r_ws = _with_workspace(r, v, cu, b, B, total, 0.99, 0.95, cuda)
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    side = torch.cuda.Stream(device=cuda)
+
+    def call(stream_ptr):
+        rc = _lib.lib.b200rl_gae_1d_nolp_misalign_noalloc(
+            _lib.ptr(r), _lib.ptr(v), _lib.ptr(cu), _lib.ptr(b), _lib.ptr(adv), _lib.ptr(ret), B, total,
+            0.99, 0.95, stream_ptr)
+        assert rc == 0, _lib.last_error()
+
+    call(_lib.stream_handle(cuda))  # warm-up: the one-time symbol lookup happens here
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(cuda)
+    for _ in range(3):
+        call(_lib.stream_handle(cuda))
+    torch.cuda.synchronize()
+    side.wait_stream(torch.cuda.current_stream(cuda))
+    adv.fill_(0)
+    torch.cuda.synchronize()
+    import ctypes
+    call(ctypes.c_void_p(side.cuda_stream))
+    side.synchronize()
+    free1, _ = torch.cuda.mem_get_info(cuda)
+    assert free1 >= free0, f"device memory shrank by {free0 - free1} bytes across allocation-free calls"
+    np.testing.assert_allclose(adv.cpu().numpy(), a_ws.cpu().numpy(), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(ret.cpu().numpy(), r_ws.cpu().numpy(), rtol=1e-5, atol=1e-5)
