@@ -252,6 +252,7 @@ def test_full_size_cfg3_loss_args_and_entropy_bonus(temp, cuda):
     lp, ent = BF.gather_logprobs_entropy(xg, labels, temp)
     old = lp.detach() + 0.3 * torch.randn(T, generator=gen, device=cuda)   # wide enough to hit both clips
     prox = lp.detach() + 0.2 * torch.randn(T, generator=gen, device=cuda)
+    prox[::37] -= 1.5  # ratio e^1.5 > c_clip on ~3 % of the tokens: the dual clip fires where A < 0
     loss, stat = BF.ppo_actor_loss_fn(lp, prox, old, adv, loss_mask=mask, **args)
     total = loss - 0.01 * ent.mean()
     total.backward()
