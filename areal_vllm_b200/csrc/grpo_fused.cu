@@ -290,6 +290,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
       const volatile float* bc = bwdc + slot * 4;
       const float nlse2 = bc[0], A0 = bc[1], lab_add = bc[2];
       const int lab = __float_as_int(bc[3]);
+      float nlse2f;
+      uint32_t sgn;
+      bwd_row_consts<E>(nlse2, A0, nlse2f, sgn);
       const int lvec = lab >= 0 ? lab / E::kPerVec : -1;
       const int lsub = lab >= 0 ? lab % E::kPerVec : 0;
       char* out_row = reinterpret_cast<char*>(p.dlogits) + ((int64_t)row * p.ld_out) * E::kBytes;
@@ -306,7 +309,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
           ws.release(lane);
 #pragma unroll
           for (int i = 0; i < 8; i++)
-            bwd_vec<E, false>(v[i], v0 + i * 32, true, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
+            bwd_vec_folded<E>(v[i], v0 + i * 32, true, scale, nlse2f, sgn, lab_add, lvec, lsub, out_row);
         } else {
           const int nr = (nv + 31) >> 5;
 #pragma unroll 1
@@ -314,7 +317,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
             const bool act = r * 32 + lane < nv;
             uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
             if (act) v = lds128(base + r * 512);
-            bwd_vec<E, false>(v, v0 + r * 32, act, scale, nlse2, A0, 0.f, lab_add, lvec, lsub, out_row);
+            bwd_vec_folded<E>(v, v0 + r * 32, act, scale, nlse2f, sgn, lab_add, lvec, lsub, out_row);
           }
           ws.release(lane);
         }

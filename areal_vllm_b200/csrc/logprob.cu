@@ -243,6 +243,9 @@ logprob_bwd_kernel(const void* __restrict__ logits, int64_t ld,
     const int row = blockIdx.x + it * gridDim.x;
     const float nlse2 = n_nlse2, A0 = n_A0, B0 = n_B0, lab_add = n_lab;
     const int lvec = n_lvec, lsub = n_lsub;
+    float nlse2f = 0.f;
+    uint32_t sgn = 0u;
+    if (!HAS_GH) bwd_row_consts<E>(nlse2, A0, nlse2f, sgn);
     if (it + 1 < nrows) load_row(row + gridDim.x, n_nlse2, n_A0, n_B0, n_lab, n_lvec, n_lsub);
     char* out_row = reinterpret_cast<char*>(dlogits) + ((int64_t)row * ld_out) * E::kBytes;
 
@@ -258,8 +261,12 @@ logprob_bwd_kernel(const void* __restrict__ logits, int64_t ld,
         for (int i = 0; i < 8; i++) v[i] = lds128(base + i * 512);
         ws.release(lane);
 #pragma unroll
-        for (int i = 0; i < 8; i++)
-          bwd_vec<E, HAS_GH>(v[i], v0 + i * 32, true, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+        for (int i = 0; i < 8; i++) {
+          if (HAS_GH)
+            bwd_vec<E, true>(v[i], v0 + i * 32, true, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+          else
+            bwd_vec_folded<E>(v[i], v0 + i * 32, true, scale, nlse2f, sgn, lab_add, lvec, lsub, out_row);
+        }
       } else {
         const int nr = (nv + 31) >> 5;
 #pragma unroll 1
@@ -267,7 +274,10 @@ logprob_bwd_kernel(const void* __restrict__ logits, int64_t ld,
           const bool act = r * 32 + lane < nv;
           uint4 v = make_uint4(kNeutral, kNeutral, kNeutral, kNeutral);
           if (act) v = lds128(base + r * 512);
-          bwd_vec<E, HAS_GH>(v, v0 + r * 32, act, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+          if (HAS_GH)
+            bwd_vec<E, true>(v, v0 + r * 32, act, scale, nlse2, A0, B0, lab_add, lvec, lsub, out_row);
+          else
+            bwd_vec_folded<E>(v, v0 + r * 32, act, scale, nlse2f, sgn, lab_add, lvec, lsub, out_row);
         }
         ws.release(lane);
       }

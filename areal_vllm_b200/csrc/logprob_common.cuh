@@ -21,6 +21,7 @@ template <int DT> struct Elem;
 template <> struct Elem<B200RL_BF16> {
   static constexpr int kPerVec = 8, kBytes = 2;
   static constexpr uint32_t kNeutralWord = 0xF14AF14Au;  // pair of ~-1e30: exp -> 0, finite products
+  static constexpr uint32_t kSignWord = 0x80008000u;     // sign bits of a packed pair
   using MaxT = uint32_t;  // packed bf16x2 running extremum
   static __device__ __forceinline__ MaxT max_init() { return kNegInf2; }
   static __device__ __forceinline__ MaxT min_init() { return kPosInf2; }
@@ -50,6 +51,7 @@ template <> struct Elem<B200RL_BF16> {
 template <> struct Elem<B200RL_FP16> {
   static constexpr int kPerVec = 8, kBytes = 2;
   static constexpr uint32_t kNeutralWord = 0xFBFFFBFFu;  // pair of -65504 (largest finite |fp16|)
+  static constexpr uint32_t kSignWord = 0x80008000u;
   using MaxT = uint32_t;  // packed f16x2
   static __device__ __forceinline__ MaxT max_init() { return 0xFC00FC00u; }
   static __device__ __forceinline__ MaxT min_init() { return 0x7C007C00u; }
@@ -96,6 +98,7 @@ template <> struct Elem<B200RL_FP16> {
 template <> struct Elem<B200RL_FP32> {
   static constexpr int kPerVec = 4, kBytes = 4;
   static constexpr uint32_t kNeutralWord = 0xF149F2CAu;  // -1e30f
+  static constexpr uint32_t kSignWord = 0x80000000u;
   using MaxT = float;
   static __device__ __forceinline__ MaxT max_init() { return -INFINITY; }
   static __device__ __forceinline__ MaxT min_init() { return INFINITY; }
@@ -351,6 +354,43 @@ __device__ __forceinline__ void bwd_vec(const uint4& v, int vi, bool act, float 
   if (act) stg_na_v4(out_row + (int64_t)vi * 16, E::pack(d));
 }
 
+// The same vector when the entropy carries no gradient (the GRPO call site): d = p * A0 with a
+// per-row constant A0, so the multiplication is folded into the exponent,
+//   p * A0 = sign(A0) * 2^(x*scale + nlse2 + log2|A0|),
+// and the sign is one XOR per packed word: one FFMA + one MUFU.EX2 per element and half a LOP,
+// instead of FFMA + MUFU + FMUL. `nlse2f` = nlse2 + log2|A0| (-inf when A0 == 0: masked rows give
+// exact zeros), `sgn` = the dtype's packed sign mask when A0 < 0, else 0 (bwd_row_consts).
+template <typename E>
+__device__ __forceinline__ void bwd_vec_folded(const uint4& v, int vi, bool act, float scale,
+                                               float nlse2f, uint32_t sgn, float lab_add, int lvec,
+                                               int lsub, char* out_row) {
+  float x[E::kPerVec], d[E::kPerVec];
+  E::unpack(v, x);
+#pragma unroll
+  for (int j = 0; j < E::kPerVec; j++) d[j] = ex2_approx(fmaf(x[j], scale, nlse2f));
+  if (vi == lvec) {  // the one-hot term of the label, one lane once per row: sign first, in fp32
+#pragma unroll
+    for (int k = 0; k < E::kPerVec; k++) {
+      if (sgn) d[k] = -d[k];
+      if (k == lsub) d[k] += lab_add;
+    }
+    if (act) stg_na_v4(out_row + (int64_t)vi * 16, E::pack(d));
+    return;
+  }
+  uint4 o = E::pack(d);
+  o.x ^= sgn;
+  o.y ^= sgn;
+  o.z ^= sgn;
+  o.w ^= sgn;
+  if (act) stg_na_v4(out_row + (int64_t)vi * 16, o);
+}
+
+// per-row constants of the folded form
+template <typename E>
+__device__ __forceinline__ void bwd_row_consts(float nlse2, float A0, float& nlse2f, uint32_t& sgn) {
+  nlse2f = nlse2 + lg2_approx(fabsf(A0));
+  sgn = A0 < 0.f ? E::kSignWord : 0u;
+}
 
 }  // namespace lp
 }  // namespace b200rl

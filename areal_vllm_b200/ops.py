@@ -138,6 +138,9 @@ def _lp_setup_context(ctx, inputs, output):
     ctx.save_for_backward(logits, labels, lse, ent)
     ctx.temperature = temperature
     ctx.need_entropy = need_entropy
+    # an unused entropy must arrive as None, not as zeros: without an entropy gradient the backward
+    # takes the cheaper kernel variant (same choice as the eager-mode node below)
+    ctx.set_materialize_grads(False)
 
 
 def _lp_backward(ctx, g_logp, g_ent, g_lse, g_max, g_min):
