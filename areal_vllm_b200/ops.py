@@ -625,7 +625,106 @@ def _loss_backward(ctx, grads):
 ppo_loss_fwd_op.register_autograd(_loss_backward, setup_context=_loss_setup_context)
 
 
+def _ppo_loss_slabs(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap):
+    """Eager-mode launcher of b200rl_ppo_loss_fwd with every output in two slabs (one fp32
+    [6, Tp], one byte [3, Tp]) and one [2] scalar pair: four allocations instead of fourteen, which
+    is most of what a call costs on the host (the kernel itself runs 3-8 us).
+    -> (loss, N, fs rows = dlogp, s_loss, s_iw, s_kl, s_bw, s_bkl; bs rows = clip, dual, bm)."""
+    shape = logp.shape
+    dev = logp.device
+    T = logp.numel()
+
+    def flat(t: Tensor, name: str) -> Tensor:
+        if t.shape != shape:
+            raise RuntimeError(f"{name} has shape {tuple(t.shape)}, expected {tuple(shape)}")
+        if t.dtype != torch.float32:
+            raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+        if not t.is_cuda:
+            raise RuntimeError(f"{name} must be on CUDA (b200rl has no CPU path)")
+        return t if t.is_contiguous() else t.contiguous()
+
+    lp, px, ol, ad = flat(logp.detach(), "logprobs"), flat(prox_logp, "proximal_logprobs"), \
+        flat(old_logp, "old_logprobs"), flat(adv, "advantages")
+    if mask.shape != shape:
+        raise RuntimeError(f"loss_mask has shape {tuple(mask.shape)}, expected {tuple(shape)}")
+    if not mask.is_cuda:
+        raise RuntimeError("loss_mask must be on CUDA (b200rl has no CPU path)")
+    mk = mask if mask.dtype == torch.bool else mask != 0
+    if not mk.is_contiguous():
+        mk = mk.contiguous()
+    Tp = (T + 63) // 64 * 64
+    fs = torch.empty((6, Tp), dtype=torch.float32, device=dev)
+    bs = torch.empty((3, Tp), dtype=torch.uint8, device=dev)
+    loss = torch.empty((), dtype=torch.float32, device=dev)
+    denom = torch.empty(1, dtype=torch.float32, device=dev)
+    ws = torch.empty(max(lib.b200rl_ppo_loss_workspace_bytes(T), 256), dtype=torch.uint8, device=dev)
+    fb, st4, bb = fs.data_ptr(), Tp * 4, bs.data_ptr()
+    f = lambda i: c_void_p(fb + i * st4)
+    b = lambda i: c_void_p(bb + i * Tp)
+    with _on(dev):
+        rc = lib.b200rl_ppo_loss_fwd(
+            ptr(lp), ptr(px), ptr(ol), ptr(ad), ptr(mk), T, float(clip_lo), float(clip_hi), float(c_clip),
+            float(cap), None, None, None, None, f(1), f(2), f(3), b(0), b(1), f(4), f(5), b(2), f(0),
+            ptr(loss), ptr(denom), ptr(ws), ws.numel(), stream_handle(dev))
+    check(rc, "b200rl_ppo_loss_fwd")
+    return loss, denom, fs, bs
+
+
 class _PpoLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap):
+        loss, denom, fs, bs = _ppo_loss_slabs(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap)
+        ctx.save_for_backward(fs, denom)
+        ctx.shape = logp.shape
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(fs, bs, denom)
+        return loss, fs, bs, denom
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        if g_loss is None:
+            return (None,) * 9
+        fs, denom = ctx.saved_tensors
+        T = 1
+        for d in ctx.shape:
+            T *= d
+        dev = fs.device
+        g = torch.empty(ctx.shape, dtype=torch.float32, device=dev)
+        gl = g_loss if g_loss.dtype == torch.float32 else g_loss.to(torch.float32)
+        with _on(dev):
+            rc = lib.b200rl_ppo_loss_bwd(c_void_p(fs.data_ptr()), ptr(gl), ptr(denom), ptr(g), T,
+                                         stream_handle(dev))
+        check(rc, "b200rl_ppo_loss_bwd")
+        return (g,) + (None,) * 8
+
+
+def ppo_loss_fwd(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap,
+                 adv_mean, adv_denom, adv_group):
+    args = (logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap, adv_mean, adv_denom,
+            adv_group)
+    if not _eager():
+        return ppo_loss_fwd_op(*args)
+    if adv_mean is not None or adv_denom is not None:  # fused advantage normalisation: the general launcher
+        if logp.requires_grad and torch.is_grad_enabled():
+            return list(_PpoLossFusedNormFn.apply(*args))
+        return _raw_ppo_loss_fwd(*args)
+    if logp.requires_grad and torch.is_grad_enabled():
+        loss, fs, bs, denom = _PpoLossFn.apply(*args[:9])
+    else:
+        loss, denom, fs, bs = _ppo_loss_slabs(*args[:9])
+    shape = logp.shape
+    T = logp.numel()
+    if fs.shape[1] != T:
+        fs, bs = fs[:, :T], bs[:, :T]
+    f = fs.unbind(0)
+    b = bs.unbind(0)
+    if len(shape) != 1:
+        f = [t.reshape(shape) for t in f]
+        b = [t.reshape(shape) for t in b]
+    return [loss, denom, f[0], fs.new_empty(0), f[1], f[2], f[3], b[0], b[1], f[4], f[5], b[2]]
+
+
+class _PpoLossFusedNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap,
                 adv_mean, adv_denom, adv_group):
@@ -641,17 +740,6 @@ class _PpoLossFn(torch.autograd.Function):
         dlogp, denom = ctx.saved_tensors
         g_lp = None if g_loss is None else _raw_ppo_loss_bwd(dlogp, g_loss, denom)
         return (g_lp,) + (None,) * 11
-
-
-def ppo_loss_fwd(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap,
-                 adv_mean, adv_denom, adv_group):
-    args = (logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_clip, cap, adv_mean, adv_denom,
-            adv_group)
-    if not _eager():
-        return ppo_loss_fwd_op(*args)
-    if logp.requires_grad and torch.is_grad_enabled():
-        return list(_PpoLossFn.apply(*args))
-    return _raw_ppo_loss_fwd(*args)
 
 
 def ppo_loss_bwd(dlogp, grad_loss, denom):

@@ -81,3 +81,35 @@ for name, note in (("prof_h1", "`python scripts/prof_h1.py 2048 h1` (T=2048 rows
     rep = f"gpurun_out/{name}.ncu-rep"
     if os.path.exists(rep):
         full(rep, f"{out_dir}/{tag}_ncu_{name[5:]}.txt", note)
+
+
+def traffic_json(out="profiles/traffic.json", rows=2048):
+    """dram__bytes_read.sum + dram__bytes_write.sum per [T, V] row of the H1 / fused kernels, from the
+    `ncu --set full` captures of this run (T = 2048 rows); bench.py multiplies by the rows of a
+    launch for `roofline.traffic`."""
+    import json
+
+    mul = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    res = {}
+    for rep, pats in (("gpurun_out/prof_h1.ncu-rep", (("logprob_bwd_kernel<0, 16, 3, 0>", "logprob_bwd_bf16_kernel_bytes_per_row"),
+                                                      ("logprob_fwd_kernel<0, 24, 2, 1, 1>", "logprob_fwd_bf16_kernel_bytes_per_row"))),
+                      ("gpurun_out/prof_fused.ncu-rep", (("grpo_fused_kernel", "grpo_fused_kernel_bytes_per_row"),))):
+        if not os.path.exists(rep):
+            continue
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rws = list(csv.reader(raw.splitlines()))
+        hdr, units = rws[0], rws[1]
+        ir, iw, ik = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+        for pat, key in pats:
+            vals = [float(r[ir].replace(",", "")) * mul[units[ir]] + float(r[iw].replace(",", "")) * mul[units[iw]]
+                    for r in rws[2:] if pat in r[ik]]
+            if vals:
+                res[key] = sum(vals) / len(vals) / rows
+    if res:
+        res["source"] = (f"scripts/summarize_prof.py {tag}: ncu --set full captures of scripts/prof_h1.py (T={rows} rows x V=151936 bf16), "
+                         "dram__bytes_read.sum + dram__bytes_write.sum averaged over the captured launches")
+        json.dump(res, open(out, "w"), indent=1)
+        print("wrote", out, res)
+
+
+traffic_json()

@@ -129,6 +129,17 @@ for T in (10240, 32768, 1 << 20):
         torch.autograd.grad(loss, lpg)
     ms = timeit(fb, flush_l2=False)
     print(f"PPO loss fwd+bwd via public API T={T:8d}: {ms*1e3:8.1f} us")
+for T, V in ((10240, 2048), (2048, 2048)):
+    g = torch.Generator(device=dev).manual_seed(1)
+    xl = (torch.randn(T, V, device=dev, generator=g) * 2).bfloat16().requires_grad_(True)
+    data = dict(input_ids=torch.randint(0, V, (T,), device=dev, generator=g), logprobs=-torch.rand(T, device=dev, generator=g),
+                advantages=torch.randn(T, device=dev, generator=g), loss_mask=(torch.rand(T, device=dev, generator=g) < 0.7).float(),
+                prox_logp=-torch.rand(T, device=dev, generator=g))
+    def gl(stats):
+        loss = pkg.actor.grpo_loss_fn(xl, data, 1.0, 0.2, 0.28, 3.0, 5.0, stats=stats)
+        torch.autograd.grad(loss, xl)
+    print(f"grpo_loss_fn fwd+bwd via public API T={T:6d} V={V} (small V: host-bound), stats dict: {timeit(lambda: gl({}), flush_l2=False)*1e3:8.1f} us"
+          f"   no stats: {timeit(lambda: gl(None), flush_l2=False)*1e3:8.1f} us")
 class Cfg: mean_level, std_level, group_size = "group", "group", 8
 x = torch.randn(512, 1024, device=dev); m = (torch.rand(512, 1024, device=dev) < 0.6).float()
 an = pkg.actor.AdvNorm(Cfg)
