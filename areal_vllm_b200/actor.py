@@ -84,6 +84,9 @@ class AdvNorm:
       group-level statistic, as in the reference (:486-494, :518-533).
 
     One moments launch per level instead of a python loop over groups; moments in fp64.
+    The constructor's argument validation (the three ValueError messages) is the reference's own
+    (actor.py:388-412), kept word for word because callers and the reference's tests
+    (areal/tests/test_adv_norm_config.py) match on it; ``__call__`` is a different algorithm.
     """
 
     def __init__(self, advNorm_cfg):

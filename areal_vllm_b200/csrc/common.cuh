@@ -44,6 +44,8 @@ inline int check_launch(const char* what) {
 }
 
 int sm_count();  // SM count of the current device (cached per device)
+// opt a kernel into `bytes` of dynamic shared memory, once per (kernel, current device); thread-safe
+int ensure_dynamic_smem(const void* kernel, int bytes);
 
 // ---- launchers shared between translation units (not part of the C ABI) ----------------------
 // logprob.cu. `roll` != 0: `labels` is the packed input_ids, row t's label is labels[(t+1) % T].

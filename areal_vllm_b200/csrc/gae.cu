@@ -315,13 +315,7 @@ int launch_serial_batched(const float* rewards, const float* values, const int32
                           float lam, cudaStream_t st) {
   constexpr size_t smem = (size_t)kBatWarps * STAGES * 2 * GS * (CH + 1) * sizeof(float);
   auto k = gae_serial_batched_kernel<GS, CH, STAGES>;
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  B200RL_CUDA(cudaGetDevice(&dev));
-  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    B200RL_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set[dev] = true;
-  }
+  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(k), (int)smem)) return rc;
   const int ngroups = (batch + GS - 1) / GS;
   int grid = (ngroups + kBatWarps - 1) / kBatWarps;
   const int cap = sm_count() * (int)(220 * 1024 / (smem + 1024));
@@ -1254,14 +1248,8 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
   if (mode == B200RL_GAE_SERIAL_BATCH8 || (mode == B200RL_GAE_SERIAL && !use_slots && short_seqs && batch >= 16384))
     return launch_serial_batched<8, 128, 2>(rewards, values, cu_seqlens, bootstrap, adv, ret, batch, gamma, lam, st);
   if (use_slots) {
-    static bool slot_attr[64] = {false};
-    int dev = 0;
-    B200RL_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !slot_attr[dev]) {
-      B200RL_CUDA(cudaFuncSetAttribute(gae_serial_slots_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)kSlotSmem));
-      slot_attr[dev] = true;
-    }
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(gae_serial_slots_kernel), (int)kSlotSmem))
+      return rc;
     unsigned int* ticket = nullptr;  // with a workspace: sequences are handed out by a ticket counter
     if (workspace && workspace_bytes >= sizeof(unsigned int) &&
         (reinterpret_cast<uintptr_t>(workspace) & 3) == 0) {
@@ -1293,18 +1281,10 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
       return B200RL_EWORKSPACE;
     }
     B200RL_CUDA(cudaMemsetAsync(workspace, 0, W.bytes, st));
-    static bool attr_set[64] = {false};
     const size_t smem = sizeof(ScanSmem) * kScanWarps;
     const size_t smem_p = sizeof(PieceSmem) * kScanWarps;
-    int dev = 0;
-    B200RL_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-      B200RL_CUDA(cudaFuncSetAttribute(gae_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem));
-      B200RL_CUDA(cudaFuncSetAttribute(gae_pieces_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem_p));
-      attr_set[dev] = true;
-    }
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(gae_scan_kernel), (int)smem)) return rc;
+    if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(gae_pieces_kernel), (int)smem_p)) return rc;
     int grid = (W.num_tiles + kScanWarps - 1) / kScanWarps;
     const int cap = sm_count() * 6;  // 6 CTAs x 4 warps x 8 KiB = 192 KiB smem per SM
     if (grid > cap) grid = cap;

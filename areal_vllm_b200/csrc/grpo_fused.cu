@@ -401,25 +401,7 @@ FusedWs fused_ws(void* ws) {
 
 template <typename K>
 int set_smem_once(K kernel, int bytes) {
-  static const void* seen_fn[32];
-  static int seen_dev[32];
-  static int n_seen = 0;
-  int dev = 0;
-  cudaGetDevice(&dev);
-  const void* fn = reinterpret_cast<const void*>(kernel);
-  for (int i = 0; i < n_seen && i < 32; i++)
-    if (seen_fn[i] == fn && seen_dev[i] == dev) return 0;
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e != cudaSuccess) {
-    set_last_error("cudaFuncSetAttribute(smem=%d): %s", bytes, cudaGetErrorString(e));
-    return (int)e;
-  }
-  if (n_seen < 32) {
-    seen_fn[n_seen] = fn;
-    seen_dev[n_seen] = dev;
-    n_seen++;
-  }
-  return 0;
+  return ensure_dynamic_smem(reinterpret_cast<const void*>(kernel), bytes);
 }
 
 template <int DT, bool MINMAX>

@@ -386,26 +386,7 @@ logprob_bwd_plain_kernel(const T* __restrict__ logits, int64_t ld, const int64_t
 
 template <typename K>
 int set_smem(K kernel, int bytes) {
-  // once per (kernel, device); a benign race at worst sets the attribute twice
-  static const void* seen_fn[64];
-  static int seen_dev[64];
-  static int n_seen = 0;
-  int dev = 0;
-  cudaGetDevice(&dev);
-  const void* fn = reinterpret_cast<const void*>(kernel);
-  for (int i = 0; i < n_seen && i < 64; i++)
-    if (seen_fn[i] == fn && seen_dev[i] == dev) return 0;
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e != cudaSuccess) {
-    set_last_error("cudaFuncSetAttribute(smem=%d): %s", bytes, cudaGetErrorString(e));
-    return (int)e;
-  }
-  if (n_seen < 64) {
-    seen_fn[n_seen] = fn;
-    seen_dev[n_seen] = dev;
-    n_seen++;
-  }
-  return 0;
+  return ensure_dynamic_smem(reinterpret_cast<const void*>(kernel), bytes);
 }
 
 // Ring geometry (one CTA per SM). Measured on B200 (scripts/gpu_tune.sh): the forward, whose body

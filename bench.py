@@ -838,8 +838,12 @@ def main_b200rl(args):
         tok = torch.tensor([float(n_tok)], device=dev, dtype=torch.float64)
         dist.all_reduce(tok)
         total_tok = float(tok.item())
+        toks = [torch.zeros_like(tok) for _ in range(world)]
+        dist.all_gather(toks, torch.tensor([float(n_tok)], device=dev, dtype=torch.float64))
+        tokens_per_rank = [int(t.item()) for t in toks]
     else:
         total_tok = float(n_tok)
+        tokens_per_rank = [n_tok]
     value = total_tok * args.steps / (elapsed_ms * 1e-3)
 
     # per-launch device times of the composite forward and of the backward chain.
@@ -1063,7 +1067,7 @@ def main_b200rl(args):
             "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "tokens_per_step_per_gpu": n_tok, "micro_batches": n_mb,
+            "config": {"workload": WORKLOAD, "tokens_per_step_per_gpu": tokens_per_rank, "micro_batches": n_mb,
                        "temperature": TEMPERATURE, "eps_clip": EPS_CLIP, "behav_imp_weight_cap": CAP,
                        "adv_norm": "group/group (8)", "parallelism": f"dp{world} (sequence-sharded, weak)",
                        "cache": f"inputs larger than L2: {N_LOGITS_BUFFERS} rotating logits buffers of "
