@@ -9,6 +9,9 @@
 //                     gae_kernel_1d_nolp_misalign. Used when gamma*lam ~ 1, where any
 //                     re-association of the fp32 suffix sum moves results by more than the
 //                     1e-5 parity bar (the sum has no forgetting, errors random-walk).
+//                     gae_serial_relay_kernel (same bits, the chain relayed lane to lane in
+//                     registers) takes over from 1024 sequences up, gae_serial_slots_kernel
+//                     (8 ticket-fed chains per warp) for very many short sequences.
 //
 //  gae_scan_kernel    the packed token stream is cut into fixed tiles of 1024 tokens, one warp
 //                     per tile, whatever the sequence lengths are (perfect balance: a 16k-token
@@ -164,6 +167,116 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
         for (int k = 0; k < kSerPerLane; k++) {
           if (32 * k >= first) {
             const float A = d[32 * k + lane];
+            ap[32 * k] = A;
+            tp[32 * k] = __fadd_rn(A, vk[k]);
+          }
+        }
+      }
+      __syncwarp();
+      hi = lo;
+    }
+  }
+}
+
+// ============================ SERIAL, relay ==================================
+// Same warp-per-sequence walk as gae_serial_kernel, but the chain never touches shared memory:
+// after the coalesced loads the 256 deltas are transposed ONCE (8 scalar stores + 2 16-byte loads
+// per lane, all 32 lanes busy) so that lane L holds the 8 consecutive tokens 8L..8L+7 in
+// registers; the recurrence then runs as a relay - lane 31 does its 8 dependent FMAs, hands X to
+// lane 30 with one shuffle, and so on down to lane 0 - in exactly the reference's order, so the
+// bits are the same. Per 256-token block that is 32 SHFL + 20 full-warp shared-memory
+// instructions instead of 128 single-lane LDS.128/STS.128 + 16, which is what the warps of
+// gae_serial_kernel queue for (mio_throttle / short_scoreboard).
+constexpr int kRelayPad = kSerBlk + (kSerBlk / 32) * 4;  // 4 floats of padding per 32: both the strided
+                                                          // scalar and the consecutive 16-byte accesses
+                                                          // are bank-conflict free
+__device__ __forceinline__ int relay_slot(int j) { return j + ((j >> 5) << 2); }
+
+#ifndef B200RL_RELAY_MINB
+#define B200RL_RELAY_MINB 7
+#endif
+__global__ void __launch_bounds__(kSerWarps * 32, B200RL_RELAY_MINB)
+gae_serial_relay_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+                        const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot,
+                        float* __restrict__ adv, float* __restrict__ ret, int batch, float gamma,
+                        float lam) {
+  static_assert(kSerPerLane == 8, "the relay owns 8 consecutive tokens per lane");
+  __shared__ __align__(16) float sm[kSerWarps][kRelayPad];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float* d = sm[w];
+  const float c = __fmul_rn(gamma, lam);  // ref gae.cu:24
+  const int nwarps = gridDim.x * kSerWarps;
+  for (int i = blockIdx.x * kSerWarps + w; i < batch; i += nwarps) {
+    const int rs = cu[i], re = cu[i + 1];
+    const int n = re - rs;
+    if (n <= 0) continue;
+    const float* rbase = rewards + rs;
+    const float* vbase = values + ((int64_t)rs + i);
+    const bool bs = boot[i] != 0;
+    float X = 0.f;  // lastgae entering the block at its top (lane 31)
+    SerBlock B;
+    int hi = n;
+    ser_load(B, rbase, vbase, hi, lane);
+    if (!bs && lane == 31) B.vn[kSerPerLane - 1] = 0.f;  // gae.cu:20-21
+    while (hi > 0) {
+      const int lo = hi - kSerBlk;
+      const int skip = lo < 0 ? -lo : 0;
+      float vk[kSerPerLane];
+#pragma unroll
+      for (int k = 0; k < kSerPerLane; k++) {
+        d[36 * k + lane] = __fsub_rn(__fmaf_rn(gamma, B.vn[k], B.r[k]), B.v[k]);  // slot 32k+lane, padded
+        vk[k] = B.v[k];
+      }
+      if (lo > 0) ser_load(B, rbase, vbase, lo, lane);
+      __syncwarp();
+      float4 e0 = *reinterpret_cast<const float4*>(d + relay_slot(8 * lane));      // tokens 8L .. 8L+3
+      float4 e1 = *reinterpret_cast<const float4*>(d + relay_slot(8 * lane + 4));  // tokens 8L+4 .. 8L+7
+      // Relay from lane 31 (top of the block) down to the lane that holds the sequence's first
+      // token, written without any predication: at EVERY step every lane re-runs its 8 FMAs on the
+      // X its upper neighbour holds at that moment. Lane 31's input is the carry, so its result is
+      // final after step 1 and never changes again; lane 30's is therefore final after step 2, and
+      // so on: after k steps lanes 31..32-k hold exactly the serial chain's values (same operands,
+      // same order, same roundings), whatever the lower lanes computed on the way. 10 instructions
+      // per step (SHFL, SEL, 8 FFMA) instead of a divergent branch around them.
+      const int steps = 32 - (skip >> 3);
+      float4 a0 = e0, a1 = e1;
+      float Xl = X;
+#pragma unroll 4
+      for (int s = 0; s < steps; ++s) {
+        float x = __shfl_down_sync(0xffffffffu, Xl, 1);
+        if (lane == 31) x = X;
+        a1.w = x = __fmaf_rn(c, x, e1.w);
+        a1.z = x = __fmaf_rn(c, x, e1.z);
+        a1.y = x = __fmaf_rn(c, x, e1.y);
+        a1.x = x = __fmaf_rn(c, x, e1.x);
+        a0.w = x = __fmaf_rn(c, x, e0.w);
+        a0.z = x = __fmaf_rn(c, x, e0.z);
+        a0.y = x = __fmaf_rn(c, x, e0.y);
+        a0.x = x = __fmaf_rn(c, x, e0.x);
+        Xl = x;
+      }
+      X = __shfl_sync(0xffffffffu, Xl, 0);  // only meaningful while the sequence continues (32 steps)
+      e0 = a0;
+      e1 = a1;
+      __syncwarp();
+      *reinterpret_cast<float4*>(d + relay_slot(8 * lane)) = e0;
+      *reinterpret_cast<float4*>(d + relay_slot(8 * lane + 4)) = e1;
+      __syncwarp();
+      float* ap = adv + rs + lo + lane;
+      float* tp = ret + rs + lo + lane;
+      if (lo >= 0) {
+#pragma unroll
+        for (int k = 0; k < kSerPerLane; k++) {
+          const float A = d[36 * k + lane];
+          ap[32 * k] = A;
+          tp[32 * k] = __fadd_rn(A, vk[k]);  // gae.cu:26
+        }
+      } else {
+        const int first = skip - lane;
+#pragma unroll
+        for (int k = 0; k < kSerPerLane; k++) {
+          if (32 * k >= first) {
+            const float A = d[36 * k + lane];
             ap[32 * k] = A;
             tp[32 * k] = __fadd_rn(A, vk[k]);
           }
@@ -339,8 +452,8 @@ int launch_serial_batched(const float* rewards, const float* values, const int32
 // chain lane computes delta itself - fma(gamma, v_next, r) - v, then fma(c, X, delta), the
 // reference's order and contractions, so the result is bit-identical - and overwrites r with adv
 // and v with ret in place; all 32 lanes then write the rows out coalesced.
-#ifndef B200RL_SLOTS_MIN_BATCH
-#define B200RL_SLOTS_MIN_BATCH 49152
+#ifndef B200RL_RELAY_MIN_BATCH
+#define B200RL_RELAY_MIN_BATCH 1024
 #endif
 constexpr int kSlots = 8;            // sequences in flight per warp
 #ifndef B200RL_SLOT_BLK
@@ -1232,17 +1345,19 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
     const float c = gamma * lam;
     mode = (c > 0.99f || !(c >= 0.f)) ? B200RL_GAE_SERIAL : B200RL_GAE_SCAN;
   }
-  // SERIAL picks among four kernels that produce the same bits (measured on B200,
-  // scripts/time_gae_modes.py, 2026-11 build):
-  //   slots   8 independent chains per warp with ticket refill: wins once there are enough sequences
-  //           to keep ~28k slots busy - >= 32k short sequences (500k x [1,64]: 84 us vs 144 us for
-  //           the 32-per-warp kernel, 216 us for warp-per-sequence), >= 48k longer ones (65,536 x
-  //           [64,2048]: 361 us vs 387 us; 131,072: 675 us vs 762 us);
+  // SERIAL picks among kernels that produce the same bits (measured on B200,
+  // scripts/time_gae_modes.py -> profiles/r02_gae_modes.txt):
+  //   relay   one warp per sequence, chain relayed lane to lane in registers: >= 1024 sequences of
+  //           >= 64 tokens on average (65,536 x [64,2048]: 253 us vs 386 us warp / 360 us slots;
+  //           8,192: 46 vs 64 us; 4,096 x [1k,16k]: 188 vs 266 us; 1,024: 18 vs 20 us);
+  //   slots   8 independent chains per warp with ticket refill: >= 32k SHORT sequences (500k x
+  //           [1,64]: 84 us vs 218 us warp / 144 us for the 32-per-warp kernel);
   //   batch8  8 sequences per warp in lock step: 16k-32k short sequences (< 64 tokens on average);
-  //   warp    one warp per sequence: everything else (few or long sequences).
+  //   warp    one warp per sequence, chain in lane 0: everything else (few or very long sequences).
   const bool short_seqs = total < (int64_t)batch * 64;
   const bool use_slots = mode == B200RL_GAE_SERIAL_SLOTS ||
-                         (mode == B200RL_GAE_SERIAL && batch >= (short_seqs ? 32768 : B200RL_SLOTS_MIN_BATCH));
+                         (mode == B200RL_GAE_SERIAL && short_seqs && batch >= 32768);
+  if (mode == B200RL_GAE_SERIAL && !short_seqs && batch >= B200RL_RELAY_MIN_BATCH) mode = B200RL_GAE_SERIAL_RELAY;
   if (mode == B200RL_GAE_SERIAL_BATCH32)
     return launch_serial_batched<32, 32, 2>(rewards, values, cu_seqlens, bootstrap, adv, ret, batch, gamma, lam, st);
   if (mode == B200RL_GAE_SERIAL_BATCH8 || (mode == B200RL_GAE_SERIAL && !use_slots && short_seqs && batch >= 16384))
@@ -1262,6 +1377,14 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
     gae_serial_slots_kernel<<<grid, kSlotWarps * 32, kSlotSmem, st>>>(
         rewards, values, cu_seqlens, bootstrap, adv, ret, batch, gamma, lam, ticket);
     return check_launch("gae_serial_slots_kernel");
+  }
+  if (mode == B200RL_GAE_SERIAL_RELAY) {
+    int grid = (batch + kSerWarps - 1) / kSerWarps;
+    const int cap = sm_count() * 16;
+    if (grid > cap) grid = cap;
+    gae_serial_relay_kernel<<<grid, kSerWarps * 32, 0, st>>>(rewards, values, cu_seqlens, bootstrap, adv,
+                                                            ret, batch, gamma, lam);
+    return check_launch("gae_serial_relay_kernel");
   }
   if (mode == B200RL_GAE_SERIAL || mode == B200RL_GAE_SERIAL_WARP) {
     int grid = (batch + kSerWarps - 1) / kSerWarps;

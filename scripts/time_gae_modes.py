@@ -13,7 +13,7 @@ def timeit(fn, iters=8, warm=2):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record(); torch.cuda.synchronize(); ts.append(e0.elapsed_time(e1))
     return float(np.median(ts))
-MODES = {"scan": 2, "warp": 3, "bat8": 4, "slots": 6}
+MODES = {"scan": 2, "warp": 3, "relay": 7, "slots": 6}
 def case(B, lo, hi, gl=(1.0, 1.0)):
     rng = np.random.default_rng(B)
     lens = rng.integers(lo, hi + 1, B); total = int(lens.sum())
