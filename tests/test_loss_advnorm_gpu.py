@@ -342,3 +342,31 @@ def test_grpo_loss_fast_path_equals_op_path(T, V, mask_kind, want, dtype, cuda):
         for k in sa:
             assert sa[k].dtype == sb[k].dtype and sa[k].shape == sb[k].shape, k
             assert torch.equal(sa[k], sb[k]), k
+
+
+def test_grpo_loss_fast_path_empty_and_errors(cuda):
+    """T = 0 (an empty micro-batch after dynamic filtering) and the argument errors of the composite."""
+    from areal_vllm_b200 import actor
+
+    V = 1024
+    empty = dict(input_ids=torch.zeros(0, dtype=torch.int64, device=cuda), logprobs=torch.zeros(0, device=cuda),
+                 advantages=torch.zeros(0, device=cuda), loss_mask=torch.zeros(0, device=cuda),
+                 prox_logp=torch.zeros(0, device=cuda))
+    x = torch.zeros(0, V, dtype=torch.bfloat16, device=cuda, requires_grad=True)
+    st = {}
+    loss = actor.grpo_loss_fn(x, empty, 1.0, 0.2, None, None, 5.0, stats=st)
+    assert loss.item() == 0.0 and st["new_logp"].shape == (0,) and st["n_valid_tokens"].dtype == torch.bool
+    loss.backward()
+    assert x.grad.shape == (0, V)
+    # wrong lengths / devices raise RuntimeError like the reference's TORCH_CHECKs
+    T = 16
+    good = dict(input_ids=torch.zeros(T, dtype=torch.int64, device=cuda), logprobs=torch.zeros(T, device=cuda),
+                advantages=torch.zeros(T, device=cuda), loss_mask=torch.ones(T, device=cuda),
+                prox_logp=torch.zeros(T, device=cuda))
+    xl = torch.randn(T, V, device=cuda).bfloat16()
+    for key, bad in (("advantages", torch.zeros(T + 1, device=cuda)), ("loss_mask", torch.ones(T - 1, device=cuda)),
+                     ("prox_logp", torch.zeros(T))):
+        with pytest.raises(RuntimeError):
+            actor.grpo_loss_fn(xl, {**good, key: bad}, 1.0, 0.2, None, None, 5.0)
+    with pytest.raises(AssertionError):
+        actor.grpo_loss_fn(xl, good, 1.0, 0.2, None, 0.5, 5.0)  # c_clip must be > 1 (functional.py:157)
