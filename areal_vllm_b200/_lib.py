@@ -110,6 +110,13 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_int32, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "b200rl_tp_exchange_bytes": (c_size_t, [c_int32, c_int64]),
+    "b200rl_tp_push": (c_int, [c_void_p, c_int64, c_void_p, c_int32, c_int32, c_int64, ctypes.c_uint32, c_void_p]),
+    "b200rl_tp_combine": (
+        c_int,
+        [c_void_p, c_int32, c_int64, c_int64, ctypes.c_uint32, c_float, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_void_p],
+    ),
     "b200rl_gae_2d_olp": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32,

@@ -422,27 +422,8 @@ logprob_shard_combine_kernel(const float* __restrict__ partials, int n_shards, i
                              float* __restrict__ rowmin) {
   const int64_t row = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (row >= T) return;
-  const float4* base = reinterpret_cast<const float4*>(partials);
-  float M = -INFINITY;
-  for (int k = 0; k < n_shards; k++) M = fmaxf(M, base[((int64_t)k * T + row) * 2].x);
-  float S = 0.f, W = 0.f, xy = __int_as_float(0x7fc00000), mx = -INFINITY, mn = INFINITY;
-  for (int k = 0; k < n_shards; k++) {
-    const float4 a = base[((int64_t)k * T + row) * 2];
-    const float4 b = base[((int64_t)k * T + row) * 2 + 1];
-    const float d = a.x - M;  // <= 0
-    const float f = ex2_approx(d);
-    S = fmaf(a.y, f, S);
-    W = fmaf(f, fmaf(d, a.y, a.z), W);
-    if (a.w == a.w) xy = a.w;  // the one shard that owns the label column
-    mx = fmaxf(mx, b.x);
-    mn = fminf(mn, b.y);
-  }
-  const float l2s = log2f(S);
-  lse[row] = (M + l2s) * kLn2;
-  logp[row] = (fmaf(xy, scale, -M) - l2s) * kLn2;
-  if (ent) ent[row] = kLn2 * (l2s - W / S);
-  if (rowmax) rowmax[row] = mx;
-  if (rowmin) rowmin[row] = mn;
+  combine_shard_row(reinterpret_cast<const float4*>(partials), n_shards, T, row, scale, logp, ent, lse, rowmax,
+                    rowmin);
 }
 
 template <int DT, bool ENT, bool MINMAX>

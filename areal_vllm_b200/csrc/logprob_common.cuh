@@ -385,6 +385,37 @@ __device__ __forceinline__ void bwd_vec_folded(const uint4& v, int vi, bool act,
   if (act) stg_na_v4(out_row + (int64_t)vi * 16, o);
 }
 
+// Vocabulary-parallel combine of one row: folds the n_shards 8-float records
+// (M, S, W, x_y, max, min, -, -) with the algebra the warps use inside a row. `base` is
+// [n_shards][shard_stride_rows][2] float4; shard k's record of `row` is base[(k*stride + row)*2].
+__device__ __forceinline__ void combine_shard_row(const float4* base, int n_shards,
+                                                  int64_t shard_stride_rows, int64_t row, float scale,
+                                                  float* __restrict__ logp, float* __restrict__ ent,
+                                                  float* __restrict__ lse, float* __restrict__ rowmax,
+                                                  float* __restrict__ rowmin) {
+  float M = -INFINITY;
+  // __ldcg: straight from L2 - the records may have been written by other GPUs moments ago
+  for (int k = 0; k < n_shards; k++) M = fmaxf(M, __ldcg(base + ((int64_t)k * shard_stride_rows + row) * 2).x);
+  float S = 0.f, W = 0.f, xy = __int_as_float(0x7fc00000), mx = -INFINITY, mn = INFINITY;
+  for (int k = 0; k < n_shards; k++) {
+    const float4 a = __ldcg(base + ((int64_t)k * shard_stride_rows + row) * 2);
+    const float4 b = __ldcg(base + ((int64_t)k * shard_stride_rows + row) * 2 + 1);
+    const float d = a.x - M;  // <= 0
+    const float f = ex2_approx(d);
+    S = fmaf(a.y, f, S);
+    W = fmaf(f, fmaf(d, a.y, a.z), W);
+    if (a.w == a.w) xy = a.w;  // the one shard that owns the label column
+    mx = fmaxf(mx, b.x);
+    mn = fminf(mn, b.y);
+  }
+  const float l2s = log2f(S);
+  lse[row] = (M + l2s) * kLn2;
+  logp[row] = (fmaf(xy, scale, -M) - l2s) * kLn2;
+  if (ent) ent[row] = kLn2 * (l2s - W / S);
+  if (rowmax) rowmax[row] = mx;
+  if (rowmin) rowmin[row] = mn;
+}
+
 // per-row constants of the folded form
 template <typename E>
 __device__ __forceinline__ void bwd_row_consts(float nlse2, float A0, float& nlse2f, uint32_t& sgn) {

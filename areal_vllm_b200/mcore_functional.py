@@ -64,14 +64,117 @@ def gather_partials(partial: torch.Tensor, group=None) -> torch.Tensor:
     return out.view((n,) + tuple(partial.shape))
 
 
+class PeerExchange:
+    """The forward's one exchange as peer stores instead of an NCCL all-gather (one node).
+
+    Every rank of ``group`` owns a small buffer (flags + two slots of ``[tp, max_tokens, 8]`` fp32
+    records) that all other ranks map through CUDA IPC. A call then is: shard kernel ->
+    ``b200rl_tp_push`` (32-byte records stored straight into every rank's buffer over NVLink, flag
+    behind a system-scope fence) -> ``b200rl_tp_combine`` (waits in-kernel for the tp flags of its
+    rows, then folds the records). No collective launch, no host round trip; at tp = 8 and a few
+    thousand tokens per micro-batch the all-gather's launch was most of the step.
+
+    Collective constructor (every rank of the group, same ``max_tokens``). Calls must be issued in
+    the same order on all ranks, like any collective. ``check()`` syncs and raises if a combine
+    ever timed out waiting for a peer (the kernel gives up after ~2 s instead of hanging)."""
+
+    def __init__(self, group=None, max_tokens: int = 65536, device=None):
+        import ctypes
+
+        from . import _lib
+        from .dist import PeerBuffer, export_buffer
+
+        self.group = group
+        self.tp = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.max_tokens = int(max_tokens)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        nbytes = _lib.lib.b200rl_tp_exchange_bytes(self.tp, self.max_tokens)
+        if nbytes == 0:
+            raise RuntimeError(f"unsupported exchange shape tp={self.tp}, max_tokens={max_tokens}")
+        self.buf = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize(dev)  # zero-filled before any peer can push into it
+        handles = [None] * self.tp
+        dist.all_gather_object(handles, export_buffer(self.buf), group=group)
+        self._peers, ptrs = [], []
+        for r in range(self.tp):
+            if r == self.rank:
+                ptrs.append(self.buf.data_ptr())
+            else:
+                pb = PeerBuffer(*handles[r], dev)
+                self._peers.append(pb)
+                ptrs.append(pb.data_ptr())
+        self.ptrs = (ctypes.c_void_p * self.tp)(*ptrs)
+        self.epoch = 0
+        dist.barrier(group=group)  # every rank has mapped every buffer
+
+    def exchange_and_combine(self, partial, temperature, need_entropy, need_minmax):
+        """partial [T, 8] of this rank -> (logp, entropy or empty, lse, rowmax or empty, rowmin or empty)."""
+        from . import _lib
+        from ._lib import check, lib, ptr, stream_handle
+
+        T = partial.shape[0]
+        if T > self.max_tokens:
+            raise RuntimeError(f"{T} tokens exceed the exchange buffer's {self.max_tokens}")
+        dev = partial.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        logp, lse = torch.empty(T, **f32), torch.empty(T, **f32)
+        ent = torch.empty(T if need_entropy else 0, **f32)
+        rmax = torch.empty(T if need_minmax else 0, **f32)
+        rmin = torch.empty(T if need_minmax else 0, **f32)
+        self.epoch += 1
+        st = stream_handle(dev)
+        check(lib.b200rl_tp_push(ptr(partial), T, self.ptrs, self.tp, self.rank, self.max_tokens, self.epoch, st),
+              "b200rl_tp_push")
+        check(lib.b200rl_tp_combine(ptr(self.buf), self.tp, T, self.max_tokens, self.epoch, float(temperature),
+                                    ptr(logp), ptr(ent) if need_entropy else None, ptr(lse),
+                                    ptr(rmax) if need_minmax else None, ptr(rmin) if need_minmax else None,
+                                    ptr(self.status), st), "b200rl_tp_combine")
+        return logp, ent, lse, rmax, rmin
+
+    def check(self) -> None:
+        if int(self.status.item()) != 0:
+            raise RuntimeError("a vocabulary-parallel combine timed out waiting for a peer's records")
+
+    def close(self) -> None:
+        for pb in self._peers:
+            pb.close()
+        self._peers = []
+
+
+_EXCHANGES: Dict = {}
+
+
+def enable_peer_exchange(group=None, max_tokens: int = 65536) -> PeerExchange:
+    """Collective over ``group``: from now on ``vocab_parallel_*`` calls on this group exchange
+    their records through peer memory (``PeerExchange``) instead of NCCL, for micro-batches of up
+    to ``max_tokens`` tokens (larger ones fall back to the all-gather)."""
+    group = dist.group.WORLD if group is None else group
+    ex = PeerExchange(group, max_tokens)
+    _EXCHANGES[group] = ex
+    return ex
+
+
+def disable_peer_exchange(group=None) -> None:
+    group = dist.group.WORLD if group is None else group
+    ex = _EXCHANGES.pop(group, None)
+    if ex is not None:
+        ex.close()
+
+
 class _VocabParallelLogprobEntropy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, shard, labels, temperature, group, vocab_start, need_entropy, need_minmax):
         local = (labels - vocab_start).contiguous()
         mm = bool(need_minmax)
         partial = ops._raw_logprob_shard_fwd(shard, local, temperature, need_entropy, mm)
-        logp, ent, lse, rmax, rmin = ops._raw_logprob_shard_combine(
-            gather_partials(partial, group), temperature, need_entropy, mm)
+        ex = _EXCHANGES.get(group) if group is not None else None
+        if ex is not None and partial.shape[0] <= ex.max_tokens and partial.shape[0] <= 262144:
+            logp, ent, lse, rmax, rmin = ex.exchange_and_combine(partial, temperature, need_entropy, mm)
+        else:
+            logp, ent, lse, rmax, rmin = ops._raw_logprob_shard_combine(
+                gather_partials(partial, group), temperature, need_entropy, mm)
         ctx.save_for_backward(shard, local, lse, ent)
         ctx.temperature = temperature
         ctx.need_entropy = need_entropy

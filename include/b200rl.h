@@ -128,6 +128,27 @@ int b200rl_logprob_shard_combine(const float* partials, int32_t n_shards, int64_
                                  float temperature, float* logp, float* entropy, float* lse,
                                  float* rowmax, float* rowmin, void* stream);
 
+/* The exchange of the [T, 8] records WITHOUT a collective library call: peer stores over NVLink into
+ * a buffer that every rank of the tensor-parallel group (one node) has mapped, e.g. with
+ * b200rl_ipc_export / b200rl_ipc_open. No counterpart in the reference, which all-reduces.
+ *   b200rl_tp_exchange_bytes(tp, max_tokens): size of one rank's buffer (flags + two record slots);
+ *     zero-fill it once, before any rank's first push (the caller synchronises that).
+ *   b200rl_tp_push: stores this rank's `partial` [T, 8] into slot (epoch & 1) of EVERY rank's
+ *     buffer (`peer_bufs[r]` = rank r's buffer as mapped in THIS process, r = rank is the local
+ *     one), then publishes `epoch` in its flags behind a system-scope fence.
+ *   b200rl_tp_combine: waits (inside the kernel, bounded to ~2 s, then *status = 1) until every
+ *     rank's records of `epoch` have arrived in `my_buf`, then computes the outputs of
+ *     b200rl_logprob_shard_combine. `status` is a DEVICE int32 the caller zeroes once.
+ * All ranks call push/combine in the same order with epoch = 1, 2, 3, ...; T <= max_tokens and
+ * <= 262,144 rows per call, tp <= 16. Two slots suffice because a rank can be at most one call
+ * ahead of a peer (its combine of call e needs the peer's push of call e). */
+size_t b200rl_tp_exchange_bytes(int32_t tp, int64_t max_tokens);
+int b200rl_tp_push(const float* partial, int64_t T, void* const* peer_bufs, int32_t tp, int32_t rank,
+                   int64_t max_tokens, uint32_t epoch, void* stream);
+int b200rl_tp_combine(void* my_buf, int32_t tp, int64_t T, int64_t max_tokens, uint32_t epoch,
+                      float temperature, float* logp, float* entropy, float* lse, float* rowmax,
+                      float* rowmin, int32_t* status, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * H1+H2 fused: the whole GRPO actor step on one packed micro-batch in ONE pass over HBM.
  * ref: areal/engine/ppo/actor.py:292-367 (grpo_loss_fn) followed by loss.backward()

@@ -15,16 +15,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from areal_vllm_b200 import functional, mcore_functional  # noqa: E402
 
 
-def run(dev, rank, world, T=4096, V=151936, group=None):
-    """Collective over the (already initialised) default group; returns the result dict on every
-    rank ("ok" is the AND over ranks). bench.py --gpus N calls this for its `parity.tp` entry."""
-    group = dist.group.WORLD if group is None else group
-    assert V % world == 0
-    gen = torch.Generator(device=dev).manual_seed(7)
-    full = (torch.randn(T, V, generator=gen, device=dev) * 2).bfloat16()
-    labels = torch.randint(0, V, (T,), generator=gen, device=dev)
-    g1 = torch.randn(T, generator=gen, device=dev)
-    g2 = torch.randn(T, generator=gen, device=dev) * 0.1
+def _one(dev, rank, world, T, V, group, full, labels, g1, g2):
     Vs = V // world
     shard = full[:, rank * Vs:(rank + 1) * Vs].contiguous().requires_grad_(True)
     lp, ent = mcore_functional.vocab_parallel_logprobs_entropy(shard, labels, 0.9, group=group)
@@ -42,10 +33,10 @@ def run(dev, rank, world, T=4096, V=151936, group=None):
     gs, gr = shard.grad.float(), ref_in.grad[:, rank * Vs:(rank + 1) * Vs].float()
     err["grad_ulp_viol"] = int(((gs - gr).abs() > 2.0 ** -7 * gr.abs() + 1e-6).sum())
     ok = err["logp"] < 2e-5 and err["ent"] < 2e-5 and err["grad"] < 1e-3 and err["grad_ulp_viol"] == 0
+    del ref_in
     # timing: sharded fwd+bwd (max over ranks)
-    del ref_in, full
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    for it in range(8):
+    for it in range(13):
         if it == 3:
             dist.barrier(group=group)
             torch.cuda.synchronize()
@@ -55,15 +46,45 @@ def run(dev, rank, world, T=4096, V=151936, group=None):
         ((lp * g1).sum() + (ent * g2).sum()).backward()
     ev[1].record()
     torch.cuda.synchronize()
-    ms = torch.tensor([ev[0].elapsed_time(ev[1]) / 5, 0.0 if ok else 1.0, err["logp"], err["ent"], err["grad"],
+    ms = torch.tensor([ev[0].elapsed_time(ev[1]) / 10, 0.0 if ok else 1.0, err["logp"], err["ent"], err["grad"],
                        float(err["grad_ulp_viol"])], device=dev, dtype=torch.float64)
     if ms.device.type == "cuda" and dist.get_backend(group) == "gloo":
         ms = ms.cpu()
     dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
-    return dict(tp=world, T=T, V=V, ok=bool(ms[1].item() == 0),
+    return dict(ok=bool(ms[1].item() == 0),
                 max_abs_err=dict(logp=float(ms[2]), ent=float(ms[3]), grad=float(ms[4]), grad_ulp_viol=int(ms[5])),
                 fwd_bwd_ms=float(ms[0]), tokens_per_s=T / float(ms[0]) * 1e3,
                 shard_GBps=6 * Vs * T / float(ms[0]) / 1e6)
+
+
+def run(dev, rank, world, T=4096, V=151936, group=None):
+    """Collective over the (already initialised) default group; returns the result dict on every
+    rank ("ok" is the AND over ranks and over both transports). The exchange of the [T, 8] records is
+    checked and timed twice: through the group's all-gather (NCCL, or gloo when the ranks share a
+    GPU) and through peer stores into IPC-mapped buffers (mcore_functional.PeerExchange).
+    bench.py --gpus N calls this for its `parity.tp` entry."""
+    group = dist.group.WORLD if group is None else group
+    assert V % world == 0
+    gen = torch.Generator(device=dev).manual_seed(7)
+    full = (torch.randn(T, V, generator=gen, device=dev) * 2).bfloat16()
+    labels = torch.randint(0, V, (T,), generator=gen, device=dev)
+    g1 = torch.randn(T, generator=gen, device=dev)
+    g2 = torch.randn(T, generator=gen, device=dev) * 0.1
+    res = dict(tp=world, T=T, V=V)
+    res["all_gather"] = _one(dev, rank, world, T, V, group, full, labels, g1, g2)
+    try:
+        ex = mcore_functional.enable_peer_exchange(group, max_tokens=max(T, 256))
+        res["peer_stores"] = _one(dev, rank, world, T, V, group, full, labels, g1, g2)
+        ex.check()
+        mcore_functional.disable_peer_exchange(group)
+    except Exception as e:  # a box without peer access keeps the all-gather path
+        res["peer_stores"] = dict(ok=False, error=repr(e)[:300])
+    res["ok"] = bool(res["all_gather"]["ok"] and res["peer_stores"].get("ok"))
+    # headline numbers of the entry = the faster transport
+    best = min((r for r in (res["all_gather"], res["peer_stores"]) if "fwd_bwd_ms" in r), key=lambda r: r["fwd_bwd_ms"])
+    res.update(max_abs_err=best["max_abs_err"], fwd_bwd_ms=best["fwd_bwd_ms"], tokens_per_s=best["tokens_per_s"],
+               shard_GBps=best["shard_GBps"])
+    return res
 
 
 def main():

@@ -172,3 +172,45 @@ def test_shard_errors(cuda):
     p = ops._raw_logprob_shard_fwd(x, y - 5, 1.0, True, True)
     out = ops._raw_logprob_shard_combine(p.unsqueeze(0), 1.0, True, True)
     assert torch.isnan(out[0]).all() and torch.isfinite(out[1]).all()
+
+
+@pytest.mark.parametrize("tp,T", [(2, 300), (8, 1000), (3, 1)])
+def test_peer_store_exchange_single_process(tp, T, cuda):
+    """b200rl_tp_push / b200rl_tp_combine with one GPU playing every rank: each "rank" owns an
+    exchange buffer, pushes its records into all of them, and every buffer's combine must give the
+    same bits as b200rl_logprob_shard_combine on the stacked records - on two calls in a row (the two
+    slots alternate), with the second call shorter than the first (stale rows stay behind)."""
+    import ctypes
+
+    from areal_vllm_b200 import _lib, ops
+
+    lib = _lib.lib
+    V, max_tokens = 4096, 1024
+    Vs = (V // tp) // 8 * 8
+    nbytes = lib.b200rl_tp_exchange_bytes(tp, max_tokens)
+    assert nbytes > 0 and lib.b200rl_tp_exchange_bytes(17, 10) == 0
+    bufs = [torch.zeros(nbytes, dtype=torch.uint8, device=cuda) for _ in range(tp)]
+    ptrs = (ctypes.c_void_p * tp)(*[b.data_ptr() for b in bufs])
+    status = torch.zeros(1, dtype=torch.int32, device=cuda)
+    st = _lib.stream_handle(cuda)
+    gen = torch.Generator().manual_seed(tp * 1000 + T)
+    for epoch, Tc in ((1, T), (2, max(T // 2, 1)), (3, T)):
+        x = (torch.randn(Tc, Vs * tp, generator=gen) * 2).bfloat16().to(cuda)
+        y = torch.randint(0, Vs * tp, (Tc,), generator=gen).to(cuda)
+        parts = [ops._raw_logprob_shard_fwd(x[:, r * Vs:(r + 1) * Vs].contiguous(), (y - r * Vs).contiguous(), 0.8, True, True)
+                 for r in range(tp)]
+        want = ops._raw_logprob_shard_combine(torch.stack(parts), 0.8, True, True)
+        for r in range(tp):
+            rc = lib.b200rl_tp_push(_lib.ptr(parts[r]), Tc, ptrs, tp, r, max_tokens, epoch, st)
+            assert rc == 0, _lib.last_error()
+        for r in range(tp):
+            outs = [torch.empty(Tc, device=cuda) for _ in range(5)]
+            rc = lib.b200rl_tp_combine(_lib.ptr(bufs[r]), tp, Tc, max_tokens, epoch, 0.8, *[_lib.ptr(o) for o in outs],
+                                       _lib.ptr(status), st)
+            assert rc == 0, _lib.last_error()
+            for got, ref in zip(outs, want):
+                assert torch.equal(got, ref)
+    assert int(status.item()) == 0
+    # argument errors: too many rows for the buffer, epoch 0
+    assert lib.b200rl_tp_push(_lib.ptr(parts[0]), max_tokens + 1, ptrs, tp, 0, max_tokens, 4, st) == -1
+    assert lib.b200rl_tp_push(_lib.ptr(parts[0]), T, ptrs, tp, 0, max_tokens, 0, st) == -1
