@@ -70,6 +70,16 @@ SIGNATURES = {
          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,  # 8 stats
          c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],  # dlogits, ld_out, loss, denom, ws
     ),
+    "b200rl_grpo_fused_step_ids": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_void_p, c_int, c_int64, c_int64, c_float,   # logits..temperature
+         c_void_p, c_void_p, c_void_p, c_void_p, c_int,                          # prox, old, adv, mask, mask_is_f32
+         c_float, c_float, c_float, c_float, c_void_p,                           # clip_lo/hi, c_clip, cap, upstream
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,                       # logp, entropy, lse, rowmax, rowmin
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,  # 8 stats
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,                       # valid, 2 ratios, 2 clipped logp
+         c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],   # dlogits, ld_out, loss, denom, ws
+    ),
     "b200rl_scale_inplace": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p]),
     "b200rl_gae_workspace_bytes": (c_size_t, [c_int32, c_int64]),
     "b200rl_gae_1d_nolp_misalign": (

@@ -311,45 +311,45 @@ def grpo_loss_fn_fused(
     input_ids = input_data["input_ids"]
     old_logp = input_data["logprobs"]
     advantages = input_data["advantages"]
-    loss_mask = input_data["loss_mask"].bool()
     prox_logp = input_data["prox_logp"]
-    want_stats = stats is not None or _stats_tracker() is not None
+    st = _stats_tracker()
+    want_stats = stats is not None or st is not None
     out = None
-    if logits.is_cuda and logits.dim() == 2 and logits.requires_grad and torch.is_grad_enabled() \
-            and not torch.compiler.is_compiling():
-        labels = torch.roll(input_ids, shifts=-1, dims=-1)
+    if (logits.is_cuda and logits.dim() == 2 and logits.requires_grad and torch.is_grad_enabled()
+            and input_ids.dim() == 1 and input_ids.dtype == torch.int64 and input_ids.is_contiguous()
+            and logits.stride(1) == 1 and not torch.compiler.is_compiling()):
         if c_clip is not None:
             assert c_clip > 1.0, c_clip
         up = None
         if loss_scale is not None:
             up = loss_scale if isinstance(loss_scale, torch.Tensor) else torch.tensor(
                 float(loss_scale), dtype=torch.float32, device=logits.device)
-        out = _ops._raw_grpo_fused_step(
-            logits.detach(), labels, prox_logp, old_logp, advantages, loss_mask, float(temperature),
-            1.0 - eps_clip, 1.0 + (eps_clip if eps_clip_higher is None else eps_clip_higher),
+        # one host call: mask count + the fused kernel; the label roll, the mask cast and the logged
+        # tensors all happen inside it (csrc/grpo_fused.cu, b200rl_grpo_fused_step_ids)
+        out = _ops._raw_grpo_fused_step_ids(
+            logits.detach(), input_ids, True, prox_logp, old_logp, advantages, input_data["loss_mask"],
+            float(temperature), 1.0 - eps_clip, 1.0 + (eps_clip if eps_clip_higher is None else eps_clip_higher),
             -1.0 if c_clip is None else float(c_clip),
-            -1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap), up, True)
+            -1.0 if behav_imp_weight_cap is None else float(behav_imp_weight_cap), up, want_stats)
     if out is None:
         loss = grpo_loss_fn(logits, input_data, temperature, eps_clip, eps_clip_higher, c_clip,
                             behav_imp_weight_cap, stats=stats)
         return loss * loss_scale if loss_scale is not None else loss
-    loss = _ops._GrpoFusedFn.apply(logits, out["loss"], out["dlogits"], up)
+    loss_unscaled, dlogits, r, up = out
+    loss = _ops._GrpoFusedFn.apply(logits, loss_unscaled, dlogits, up)
     if want_stats:
-        clip_mask = out["s_clip"].view(torch.bool)
-        dual = out["s_dual"].view(torch.bool)
         collected = dict(
-            n_valid_tokens=loss_mask, clipped_tokens=clip_mask, dual_clipped_tokens=dual,
-            importance_weight=out["s_iw"], approx_kl=out["s_kl"], new_logp=out["logp"],
-            old_logp=old_logp, entropy=out["entropy"], actor_loss=out["s_loss"],
-            clip_ratio=clip_mask.float(), dual_clip_ratio=dual.float(),
-            unclipped_behave_tokens=out["s_bm"].view(torch.bool), behave_imp_weight=out["s_bw"],
-            behave_approx_kl=out["s_bkl"], vocab_min_logits=out["rowmin"], vocab_max_logits=out["rowmax"],
-            clipped_new_logp=torch.where(clip_mask, out["logp"], 0.0),
-            clipped_old_logp=torch.where(clip_mask, old_logp, 0.0),
+            n_valid_tokens=r["valid"], clipped_tokens=r["s_clip"], dual_clipped_tokens=r["s_dual"],
+            importance_weight=r["s_iw"], approx_kl=r["s_kl"], new_logp=r["logp"], old_logp=old_logp,
+            entropy=r["entropy"], actor_loss=r["s_loss"], clip_ratio=r["clip_ratio"],
+            dual_clip_ratio=r["dual_clip_ratio"], unclipped_behave_tokens=r["s_bm"],
+            behave_imp_weight=r["s_bw"], behave_approx_kl=r["s_bkl"], vocab_min_logits=r["rowmin"],
+            vocab_max_logits=r["rowmax"], clipped_new_logp=r["clipped_new_logp"],
+            clipped_old_logp=r["clipped_old_logp"],
         )
         if stats is not None:
             stats.update(collected)
-        _register_stats(_stats_tracker(), logits, collected)
+        _register_stats(st, logits, collected)
     return loss
 
 

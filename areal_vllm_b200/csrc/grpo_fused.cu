@@ -59,7 +59,9 @@ struct FusedParams {
   int T, V;
   float scale, inv_temp;
   const float *prox, *old, *adv;
-  const uint8_t* mask;
+  const uint8_t* mask;     // bytes (torch.bool) ...
+  const float* mask_f32;   // ... or fp32 (non-zero = valid) when mask == nullptr
+  int roll;                // labels = input_ids, label of row t = labels[(t+1) % T]
   float clip_lo, clip_hi, c_clip, cap;
   const float* denom;     // N = max(count(mask), 1), device
   const float* upstream;  // loss scale known in advance, device, may be null (= 1)
@@ -68,6 +70,9 @@ struct FusedParams {
   uint8_t *s_clip, *s_dual;
   float *s_bw, *s_bkl;
   uint8_t* s_bm;
+  // the derived tensors grpo_loss_fn logs (actor.py:339-365), all nullable
+  uint8_t* s_valid;
+  float *s_clip_ratio, *s_dual_ratio, *s_clip_new, *s_clip_old;
   void* dlogits;
   int64_t ld_out;
   double* partial;        // [grid][2]
@@ -76,10 +81,15 @@ struct FusedParams {
 };
 
 __global__ void __launch_bounds__(1024)
-mask_count_kernel(const uint8_t* __restrict__ mask, int64_t T, float* __restrict__ denom, int or_one) {
+mask_count_kernel(const uint8_t* __restrict__ mask, const float* __restrict__ mask_f32, int64_t T,
+                  float* __restrict__ denom, int or_one) {
   __shared__ int red[32];
   int c = 0;
-  for (int64_t i = threadIdx.x; i < T; i += 1024) c += mask[i] != 0;
+  if (mask) {
+    for (int64_t i = threadIdx.x; i < T; i += 1024) c += mask[i] != 0;
+  } else {
+    for (int64_t i = threadIdx.x; i < T; i += 1024) c += mask_f32[i] != 0.f;
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = c;
@@ -130,14 +140,14 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
       float xy = 0.f, t_prox = 0.f, t_old = 0.f, t_adv = 0.f, t_mask = 0.f;
       int t_lab = -1;
       if (fetch) {
-        const int64_t lab = p.labels[row];
+        const int64_t lab = p.labels[label_row(row, T, p.roll)];
         const bool ok = lab >= 0 && lab < V;
         xy = ok ? E::load1(p.logits, (int64_t)row * p.ld + lab) : __int_as_float(0x7fc00000);
         t_lab = ok ? (int)lab : -1;
         t_prox = p.prox[row];
         t_old = p.old[row];
         t_adv = p.adv[row];
-        t_mask = p.mask[row] ? 1.f : 0.f;
+        t_mask = (p.mask ? p.mask[row] != 0 : p.mask_f32[row] != 0.f) ? 1.f : 0.f;
       }
 
       // ---------------- pass 1: forward statistics (row from HBM) ----------------
@@ -242,26 +252,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
             const float l2s = log2f(Sr);
             const float lse_nat = (Mr + l2s) * kLn2;
             const float lpv = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
-            p.lse[row] = lse_nat;
-            p.logp[row] = lpv;
-            if (p.ent) p.ent[row] = kLn2 * (l2s - Tr / Sr);
-            if (MINMAX) {
-              if (p.rowmax) p.rowmax[row] = mxr;
-              if (p.rowmin) p.rowmin[row] = mnr;
-            }
             const PpoToken k = ppo_token(lpv, px, ol, A, m, p.clip_lo, p.clip_hi, p.c_clip, p.cap);
-            if (p.s_loss) p.s_loss[row] = k.pgw;
-            if (p.s_iw) p.s_iw[row] = k.ratio;
-            if (p.s_kl) p.s_kl[row] = k.kl;
-            if (p.s_clip) p.s_clip[row] = k.clip;
-            if (p.s_dual) p.s_dual[row] = k.dual;
-            if (p.s_bw) p.s_bw[row] = k.w;
-            if (p.s_bkl) p.s_bkl[row] = k.bkl;
-            if (p.s_bm) p.s_bm[row] = k.bmask;
-            if (m) {  // rows of a CTA are finalised strictly in order: a deterministic sum
-              cta_acc[0] += (double)k.pgw;
-              cta_acc[1] += 1.0;
-            }
+            // The other 23 warps of the CTA are waiting for these four numbers: publish them first,
+            // write the row's outputs to global memory afterwards (off their critical path).
             // same operation order as ppo_loss_bwd_kernel + logprob_bwd_kernel (bit-identical dlogits)
             const float glp = k.dlogp * up_over_n;
             float* bc = bwdc + slot * 4;
@@ -271,6 +264,30 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
             bc[3] = __int_as_float(lab);
             __threadfence_block();
             ready[slot] = use + 1;
+            p.lse[row] = lse_nat;
+            p.logp[row] = lpv;
+            if (p.ent) p.ent[row] = kLn2 * (l2s - Tr / Sr);
+            if (MINMAX) {
+              if (p.rowmax) p.rowmax[row] = mxr;
+              if (p.rowmin) p.rowmin[row] = mnr;
+            }
+            if (p.s_loss) p.s_loss[row] = k.pgw;
+            if (p.s_iw) p.s_iw[row] = k.ratio;
+            if (p.s_kl) p.s_kl[row] = k.kl;
+            if (p.s_clip) p.s_clip[row] = k.clip;
+            if (p.s_dual) p.s_dual[row] = k.dual;
+            if (p.s_bw) p.s_bw[row] = k.w;
+            if (p.s_bkl) p.s_bkl[row] = k.bkl;
+            if (p.s_bm) p.s_bm[row] = k.bmask;
+            if (p.s_valid) p.s_valid[row] = m;
+            if (p.s_clip_ratio) p.s_clip_ratio[row] = k.clip ? 1.f : 0.f;
+            if (p.s_dual_ratio) p.s_dual_ratio[row] = k.dual ? 1.f : 0.f;
+            if (p.s_clip_new) p.s_clip_new[row] = k.clip ? lpv : 0.f;
+            if (p.s_clip_old) p.s_clip_old[row] = k.clip ? ol : 0.f;
+            if (m) {  // rows of a CTA are finalised strictly in order: a deterministic sum
+              cta_acc[0] += (double)k.pgw;
+              cta_acc[1] += 1.0;
+            }
           }
         }
       }
@@ -436,7 +453,30 @@ int b200rl_grpo_fused_step(const void* logits, int dtype, int64_t ld, const int6
                            float* stat_behave_approx_kl, uint8_t* stat_behave_mask, void* dlogits,
                            int64_t ld_out, float* loss, float* denom, void* workspace,
                            size_t workspace_bytes, void* stream) {
+  return b200rl_grpo_fused_step_ids(logits, dtype, ld, labels, 0, T, V, temperature, prox_logp, old_logp, adv,
+                                    mask, 0, clip_lo, clip_hi, c_clip, cap, upstream, logp, entropy, lse,
+                                    rowmax, rowmin, stat_loss, stat_imp_weight, stat_approx_kl, stat_clip_mask,
+                                    stat_dual_clip_mask, stat_behave_imp_weight, stat_behave_approx_kl,
+                                    stat_behave_mask, nullptr, nullptr, nullptr, nullptr, nullptr, dlogits,
+                                    ld_out, loss, denom, workspace, workspace_bytes, stream);
+}
+
+int b200rl_grpo_fused_step_ids(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                               int label_roll, int64_t T, int64_t V, float temperature,
+                               const float* prox_logp, const float* old_logp, const float* adv,
+                               const void* mask_any, int mask_is_f32, float clip_lo, float clip_hi,
+                               float c_clip, float cap, const float* upstream, float* logp,
+                               float* entropy, float* lse, float* rowmax, float* rowmin,
+                               float* stat_loss, float* stat_imp_weight, float* stat_approx_kl,
+                               uint8_t* stat_clip_mask, uint8_t* stat_dual_clip_mask,
+                               float* stat_behave_imp_weight, float* stat_behave_approx_kl,
+                               uint8_t* stat_behave_mask, uint8_t* stat_valid, float* stat_clip_ratio,
+                               float* stat_dual_clip_ratio, float* stat_clipped_new_logp,
+                               float* stat_clipped_old_logp, void* dlogits, int64_t ld_out, float* loss,
+                               float* denom, void* workspace, size_t workspace_bytes, void* stream) {
   using namespace b200rl;
+  const uint8_t* mask = mask_is_f32 ? nullptr : static_cast<const uint8_t*>(mask_any);
+  const float* mask_f32 = mask_is_f32 ? static_cast<const float*>(mask_any) : nullptr;
   B200RL_REQUIRE(T >= 0 && V > 0, "bad shape T=%lld V=%lld", (long long)T, (long long)V);
   B200RL_REQUIRE(ld >= V && ld_out >= V, "row stride < V");
   B200RL_REQUIRE(temperature > 0.f, "temperature must be > 0, got %f", temperature);
@@ -465,14 +505,17 @@ int b200rl_grpo_fused_step(const void* logits, int dtype, int64_t ld, const int6
     B200RL_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), st));
     return B200RL_OK;
   }
-  B200RL_REQUIRE(logits && labels && prox_logp && old_logp && adv && mask && logp && lse && dlogits,
+  B200RL_REQUIRE(logits && labels && prox_logp && old_logp && adv && mask_any && logp && lse && dlogits,
                  "null pointer");
-  mask_count_kernel<<<1, 1024, 0, st>>>(mask, T, denom, cap < -2.5f ? 0 : 1);
+  mask_count_kernel<<<1, 1024, 0, st>>>(mask, mask_f32, T, denom, cap < -2.5f ? 0 : 1);
   FusedParams p;
   p.logits = logits; p.ld = ld; p.labels = labels; p.T = (int)T; p.V = (int)V;
   p.scale = (float)(1.4426950408889634 / (double)temperature);
   p.inv_temp = (float)(1.0 / (double)temperature);
-  p.prox = prox_logp; p.old = old_logp; p.adv = adv; p.mask = mask;
+  p.prox = prox_logp; p.old = old_logp; p.adv = adv; p.mask = mask; p.mask_f32 = mask_f32;
+  p.roll = label_roll != 0;
+  p.s_valid = stat_valid; p.s_clip_ratio = stat_clip_ratio; p.s_dual_ratio = stat_dual_clip_ratio;
+  p.s_clip_new = stat_clipped_new_logp; p.s_clip_old = stat_clipped_old_logp;
   p.clip_lo = clip_lo; p.clip_hi = clip_hi; p.c_clip = c_clip; p.cap = cap;
   p.denom = denom; p.upstream = upstream;
   p.logp = logp; p.ent = entropy; p.lse = lse; p.rowmax = rowmax; p.rowmin = rowmin;

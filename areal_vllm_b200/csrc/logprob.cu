@@ -30,12 +30,6 @@ using namespace lp;
 // floats per row of the vocabulary-shard partial record: (M, S, W, x_y, max, min, 0, 0)
 constexpr int kPartialStride = 8;
 
-// roll != 0: `labels` holds the packed input_ids and the label of row t is the NEXT token,
-// labels[(t + 1) % T] = torch.roll(input_ids, -1)[t] (ref areal/engine/ppo/actor.py:308)
-__device__ __forceinline__ int label_row(int row, int T, int roll) {
-  return roll ? (row + 1 == T ? 0 : row + 1) : row;
-}
-
 // ------------------------------------------------------------------------------------------
 // forward, rows 16-B aligned (bf16 / fp16 / fp32)
 // ------------------------------------------------------------------------------------------

@@ -385,6 +385,12 @@ __device__ __forceinline__ void bwd_vec_folded(const uint4& v, int vi, bool act,
   if (act) stg_na_v4(out_row + (int64_t)vi * 16, o);
 }
 
+// roll != 0: `labels` holds the packed input_ids and the label of row t is the NEXT token,
+// labels[(t + 1) % T] = torch.roll(input_ids, -1)[t] (ref areal/engine/ppo/actor.py:308)
+__device__ __forceinline__ int label_row(int row, int T, int roll) {
+  return roll ? (row + 1 == T ? 0 : row + 1) : row;
+}
+
 // Vocabulary-parallel combine of one row: folds the n_shards 8-float records
 // (M, S, W, x_y, max, min, -, -) with the algebra the warps use inside a row. `base` is
 // [n_shards][shard_stride_rows][2] float4; shard k's record of `row` is base[(k*stride + row)*2].

@@ -297,6 +297,63 @@ def _raw_grpo_fused_step(
     return o
 
 
+def _raw_grpo_fused_step_ids(
+    logits: Tensor, input_ids: Tensor, roll: bool, prox_logp: Tensor, old_logp: Tensor, adv: Tensor,
+    mask: Tensor, temperature: float, clip_lo: float, clip_hi: float, c_clip: float, cap: float,
+    upstream: Optional[Tensor], want_stats: bool,
+):
+    """The fused step with the engine-facing conveniences (label roll inside the kernel, fp32 mask
+    read as is, logged tensors written by the kernel) and slab outputs: one host call, two
+    launches (mask count + the fused kernel), five allocations.
+    -> (loss 0-d, dlogits, {row name: [T] view}) or None when the layout is not supported."""
+    _check_logits(logits, input_ids)
+    T, V = logits.shape
+    dev = logits.device
+    pv = 4 if logits.dtype == torch.float32 else 8
+    if V % pv or logits.stride(0) % pv or logits.data_ptr() % 16:
+        return None
+    px, ol, ad = _tokvec(prox_logp.detach(), T, "prox_logp"), _tokvec(old_logp.detach(), T, "logprobs"), \
+        _tokvec(adv.detach(), T, "advantages")
+    if mask.shape != (T,) or not mask.is_cuda:
+        raise RuntimeError(f"loss_mask must be a CUDA tensor of shape ({T},)")
+    if mask.dtype == torch.float32:
+        mk, mf = mask, 1
+    else:
+        mk, mf = (mask if mask.dtype == torch.bool else mask != 0), 0
+    if not mk.is_contiguous():
+        mk = mk.contiguous()
+    up = None if upstream is None else upstream.detach().to(torch.float32).reshape(1)
+    Tp = (T + 63) // 64 * 64
+    names_f = [n for n in GL_F32 if n != "dlogp"]  # logp, lse, entropy, rowmax, rowmin, 5 stats, 4 derived
+    fs = torch.empty((len(names_f), Tp), dtype=torch.float32, device=dev)
+    bs = torch.empty((len(GL_U8), Tp), dtype=torch.bool, device=dev)
+    sc = torch.empty(2, dtype=torch.float32, device=dev)
+    dlogits = torch.empty((T, V), dtype=logits.dtype, device=dev)
+    ws = torch.empty(max(lib.b200rl_grpo_fused_workspace_bytes(T), 256), dtype=torch.uint8, device=dev)
+    fb, st4, bb, sp = fs.data_ptr(), Tp * 4, bs.data_ptr(), sc.data_ptr()
+    idx = {n: i for i, n in enumerate(names_f)}
+    f = lambda n: c_void_p(fb + idx[n] * st4) if (want_stats or n in ("logp", "lse", "entropy")) else None
+    b = (lambda i: c_void_p(bb + i * Tp)) if want_stats else (lambda i: None)
+    with _on(dev):
+        rc = lib.b200rl_grpo_fused_step_ids(
+            ptr(logits), _lib.DTYPE_CODE[logits.dtype], logits.stride(0) if T > 1 else max(V, logits.stride(0)),
+            ptr(input_ids), int(roll), T, V, float(temperature), ptr(px), ptr(ol), ptr(ad), ptr(mk), mf,
+            float(clip_lo), float(clip_hi), float(c_clip), float(cap), ptr(up),
+            f("logp"), f("entropy"), f("lse"), f("rowmax"), f("rowmin"),
+            f("s_loss"), f("s_iw"), f("s_kl"), b(0), b(1), f("s_bw"), f("s_bkl"), b(2),
+            b(3), f("clip_ratio"), f("dual_clip_ratio"), f("clipped_new_logp"), f("clipped_old_logp"),
+            ptr(dlogits), V, c_void_p(sp), c_void_p(sp + 4), ptr(ws), ws.numel(), stream_handle(dev))
+    if rc == -2:  # B200RL_EUNSUPPORTED
+        return None
+    check(rc, "b200rl_grpo_fused_step_ids")
+    rows = None
+    if want_stats:
+        fv, bv = (fs, bs) if Tp == T else (fs[:, :T], bs[:, :T])
+        rows = dict(zip(names_f, fv.unbind(0)))
+        rows.update(zip(GL_U8, bv.unbind(0)))
+    return sc[0], dlogits, rows, up
+
+
 def scale_inplace_(buf: Tensor, scale: Tensor) -> Tensor:
     """buf *= scale (device scalar); launches a kernel that exits at once when scale == 1."""
     _lib.require_cuda(buf=buf, scale=scale)

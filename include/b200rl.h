@@ -183,6 +183,23 @@ int b200rl_grpo_fused_step(const void* logits, int dtype, int64_t ld, const int6
                            float* stat_behave_approx_kl, uint8_t* stat_behave_mask, void* dlogits,
                            int64_t ld_out, float* loss, float* denom, void* workspace,
                            size_t workspace_bytes, void* stream);
+/* The same step with the conveniences of b200rl_grpo_loss_fwd: `labels` may be the packed input_ids
+ * (label_roll != 0: label of row t = labels[(t+1) % T]), the mask may be fp32 (mask_is_f32), and
+ * the derived logging tensors of grpo_loss_fn (stat_valid ... stat_clipped_old_logp, nullable) are
+ * written by the kernel, so that the engine-facing wrapper launches nothing else. */
+int b200rl_grpo_fused_step_ids(const void* logits, int dtype, int64_t ld, const int64_t* labels,
+                               int label_roll, int64_t T, int64_t V, float temperature,
+                               const float* prox_logp, const float* old_logp, const float* adv,
+                               const void* mask, int mask_is_f32, float clip_lo, float clip_hi,
+                               float c_clip, float cap, const float* upstream, float* logp,
+                               float* entropy, float* lse, float* rowmax, float* rowmin,
+                               float* stat_loss, float* stat_imp_weight, float* stat_approx_kl,
+                               uint8_t* stat_clip_mask, uint8_t* stat_dual_clip_mask,
+                               float* stat_behave_imp_weight, float* stat_behave_approx_kl,
+                               uint8_t* stat_behave_mask, uint8_t* stat_valid, float* stat_clip_ratio,
+                               float* stat_dual_clip_ratio, float* stat_clipped_new_logp,
+                               float* stat_clipped_old_logp, void* dlogits, int64_t ld_out, float* loss,
+                               float* denom, void* workspace, size_t workspace_bytes, void* stream);
 int b200rl_scale_inplace(void* buf, int dtype, int64_t numel, const float* scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
