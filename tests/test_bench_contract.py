@@ -102,7 +102,7 @@ def test_round2_reference_arm_line():
     assert abs(d["value"] / own["cpu_baseline"]["value"] - 1) < 0.15
 
 
-@pytest.mark.parametrize("n", [2, 8])
+@pytest.mark.parametrize("n", [2, 4, 8])
 def test_round2_multi_gpu_lines_carry_parity(n):
     d = _load(f"r02_bench_n{n}.json")
     assert d["n_gpus"] == n and d["scaling"] == "weak"
