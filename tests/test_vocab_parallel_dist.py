@@ -24,6 +24,9 @@ def test_tp_check_two_ranks():
            "--master-addr", "127.0.0.1", "--master-port", str(port),
            os.path.join(ROOT, "scripts", "tp_check.py"), "1024"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    if r.returncode != 0 and "B200RL_ONE_GPU" in env and (
+            "busy or unavailable" in r.stderr or "exclusive" in r.stderr.lower()):
+        pytest.skip("the GPU is in exclusive-process mode: two ranks cannot share it")
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     res = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
     assert res["ok"] and res["tp"] == 2
