@@ -191,7 +191,9 @@ def ppo_actor_loss_fn(
         None,
     )
     loss = out[0]
-    det = [t.detach() for t in out]  # the reference's stats are detached / non-differentiable
+    # the reference's stats are detached; ours come back non-differentiable already (eager path),
+    # so only tensors that still carry a graph (compiled custom-op path) are detached
+    det = [t.detach() if t.requires_grad else t for t in out]
     stat = dict(
         loss=det[4],
         importance_weight=det[5],

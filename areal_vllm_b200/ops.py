@@ -711,7 +711,7 @@ def _ppo_loss_slabs(logp, prox_logp, old_logp, adv, mask, clip_lo, clip_hi, c_cl
         mk = mk.contiguous()
     Tp = (T + 63) // 64 * 64
     fs = torch.empty((6, Tp), dtype=torch.float32, device=dev)
-    bs = torch.empty((3, Tp), dtype=torch.uint8, device=dev)
+    bs = torch.empty((3, Tp), dtype=torch.bool, device=dev)  # the kernel writes 0/1 bytes
     loss = torch.empty((), dtype=torch.float32, device=dev)
     denom = torch.empty(1, dtype=torch.float32, device=dev)
     ws = torch.empty(max(lib.b200rl_ppo_loss_workspace_bytes(T), 256), dtype=torch.uint8, device=dev)

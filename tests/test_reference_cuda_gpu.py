@@ -54,6 +54,21 @@ def test_gae_vs_reference_kernel(gl, shape, cuda, ref_gae):
     np.testing.assert_allclose(t.cpu().numpy(), r_ref.cpu().numpy(), rtol=1e-5, atol=1e-5)
 
 
+@pytest.mark.parametrize("gl", [(1.0, 1.0), (0.99, 0.95)])
+@pytest.mark.parametrize("shape,kernel", [((2048, 30, 1500), "relay"), ((6000, 64, 700), "relay"),
+                                          ((33000, 1, 60), "slots"), ((20000, 1, 50), "batch8")])
+def test_gae_large_batches_vs_reference_kernel(gl, shape, kernel, cuda, ref_gae):
+    """Batch shapes that SERIAL dispatches to the relay / slots / batched kernels (gae.cu's dispatch
+    comment), and each of those kernels forced, against the reference kernel: same bits."""
+    from areal_vllm_b200 import ppo_functional as PF
+
+    r, v, cu, b = _gae_inputs(*shape, seed=37, cuda=cuda)
+    a_ref, r_ref = ref_gae.gae_1d_nolp_misalign(r, v, cu, b, gl[0], gl[1])
+    for mode in ("serial", "serial_relay", "serial_slots"):
+        a, t = PF.gae_1d_nolp_misalign(r, v, cu, b, gl[0], gl[1], mode=mode)
+        assert torch.equal(a, a_ref) and torch.equal(t, r_ref), (mode, kernel)
+
+
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
 @pytest.mark.parametrize("n", [1000, 20000])
 def test_intervals_vs_reference_kernel(dtype, n, cuda, ref_iv):
