@@ -866,7 +866,7 @@ def main_b200rl(args):
             traffic = per_row * (sum(T for _, _, T in bwd_events) / max(len(bwd_events), 1))
     achieved = bwd_bytes / (bwd_ms * 1e-3) / 1e9
     roofline = {
-        "kernel": "logprob_bwd_kernel<bf16> (loss backward folded in)", "bound": "hbm",
+        "kernel": "logprob_bwd_kernel<bf16> (tile-per-CTA, loss backward folded in)", "bound": "hbm",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         "traffic": traffic, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": bwd_bytes / max(len(bwd_events), 1),

@@ -8,7 +8,7 @@ import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "areal_vllm_b200", "libb200rl.so")
 WANT = [("logprob_fwd_kernel<0, 24, 2, 1, 1>", "logprob_fwd_kernelILi0ELi24ELi2ELb1ELb1EE"),
-        ("logprob_bwd_kernel<0, 16, 3, 0>", "logprob_bwd_kernelILi0ELi16ELi3ELb0EE"),
+        ("logprob_bwd_kernel<0, 0>", "logprob_bwd_kernelILi0ELb0EE"),
         ("grpo_fused_kernel<0, 24, 2, 1, 0>", "grpo_fused_kernelILi0ELi24ELi2ELb1ELb0EE"),
         ("gae_pieces_kernel", "gae_pieces_kernel"),
         ("gae_serial_kernel", "gae_serial_kernelE"),

@@ -91,7 +91,7 @@ def traffic_json(out="profiles/traffic.json", rows=2048):
 
     mul = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     res = {}
-    for rep, pats in (("gpurun_out/prof_h1.ncu-rep", (("logprob_bwd_kernel<0, 16, 3, 0>", "logprob_bwd_bf16_kernel_bytes_per_row"),
+    for rep, pats in (("gpurun_out/prof_h1.ncu-rep", (("logprob_bwd_kernel<0, 0>", "logprob_bwd_bf16_kernel_bytes_per_row"),
                                                       ("logprob_fwd_kernel<0, 24, 2, 1, 1>", "logprob_fwd_bf16_kernel_bytes_per_row"))),
                       ("gpurun_out/prof_fused.ncu-rep", (("grpo_fused_kernel", "grpo_fused_kernel_bytes_per_row"),))):
         if not os.path.exists(rep):
