@@ -315,18 +315,22 @@ template <typename E, bool ENT>
 __device__ __forceinline__ void accumulate_vec(LaneState<E>& L, const uint4& v, float scale) {
   float x[E::kPerVec];
   E::unpack(v, x);
+  // pairs of elements through FFMA2 / FADD2 (same roundings as the scalar forms): per pair one
+  // FFMA2 (y), two MUFU.EX2, one FADD2 (s) and, with the entropy, one FFMA2 (t)
+  const float2 sc2 = make_float2(scale, scale), nm2 = make_float2(L.negm, L.negm);
+  float2 s = make_float2(L.s0, L.s1), t = make_float2(L.t0, L.t1);
 #pragma unroll
   for (int j = 0; j < E::kPerVec; j += 2) {
-    const float y0 = fmaf(x[j], scale, L.negm);
-    const float y1 = fmaf(x[j + 1], scale, L.negm);
-    const float e0 = ex2_approx(y0);
-    const float e1 = ex2_approx(y1);
-    L.s0 += e0;
-    L.s1 += e1;
-    if (ENT) {
-      L.t0 = fmaf(e0, y0, L.t0);
-      L.t1 = fmaf(e1, y1, L.t1);
-    }
+    const float2 y = ffma2(make_float2(x[j], x[j + 1]), sc2, nm2);
+    const float2 e = make_float2(ex2_approx(y.x), ex2_approx(y.y));
+    s = fadd2(s, e);
+    if (ENT) t = ffma2(e, y, t);
+  }
+  L.s0 = s.x;
+  L.s1 = s.y;
+  if (ENT) {
+    L.t0 = t.x;
+    L.t1 = t.y;
   }
 }
 
@@ -366,8 +370,13 @@ __device__ __forceinline__ void bwd_vec_folded(const uint4& v, int vi, bool act,
                                                int lsub, char* out_row) {
   float x[E::kPerVec], d[E::kPerVec];
   E::unpack(v, x);
+  const float2 sc2 = make_float2(scale, scale), nl2 = make_float2(nlse2f, nlse2f);
 #pragma unroll
-  for (int j = 0; j < E::kPerVec; j++) d[j] = ex2_approx(fmaf(x[j], scale, nlse2f));
+  for (int j = 0; j < E::kPerVec; j += 2) {
+    const float2 y = ffma2(make_float2(x[j], x[j + 1]), sc2, nl2);
+    d[j] = ex2_approx(y.x);
+    d[j + 1] = ex2_approx(y.y);
+  }
   if (vi == lvec) {  // the one-hot term of the label, one lane once per row: sign first, in fp32
 #pragma unroll
     for (int k = 0; k < E::kPerVec; k++) {
