@@ -387,9 +387,6 @@ __device__ __forceinline__ void bwd_vec_folded(const uint4& v, int vi, bool act,
     return;
   }
   uint4 o = E::pack(d);
-#ifdef B200RL_EXP_BWD_COPY
-  o = v;  // experiment: the streaming structure alone (no math), against torch's copy kernel
-#endif
   o.x ^= sgn;
   o.y ^= sgn;
   o.z ^= sgn;
