@@ -521,12 +521,22 @@ def _raw_gae_1d_nolp_misalign(
     rewards: Tensor, values: Tensor, cu_seqlens: Tensor, bootstrap: Tensor, gamma: float,
     lam: float, mode: int,
 ) -> Tuple[Tensor, Tensor]:
-    # checks of csrc/cugae/gae.cu:36-50, minus the two .item() host syncs on cu_seqlens
-    _lib.require_cuda(rewards=rewards, values=values, cu_seqlens=cu_seqlens, bootstrap=bootstrap)
-    _lib.require_contiguous(rewards=rewards, values=values, cu_seqlens=cu_seqlens, bootstrap=bootstrap)
+    return _gae_launch(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode, False)
+
+
+def _gae_launch(rewards: Tensor, values: Tensor, cu_seqlens: Tensor, bootstrap: Tensor, gamma: float,
+                lam: float, mode: int, one_allocation: bool) -> Tuple[Tensor, Tensor]:
+    # checks of csrc/cugae/gae.cu:36-50, minus the two .item() host syncs on cu_seqlens. Written out
+    # inline and in this order because at BASELINE config 1 (256 sequences) the kernels take ~5 us
+    # and everything the host does before the launch is on the measured path.
+    if not (rewards.is_cuda and values.is_cuda and cu_seqlens.is_cuda and bootstrap.is_cuda):
+        _lib.require_cuda(rewards=rewards, values=values, cu_seqlens=cu_seqlens, bootstrap=bootstrap)
+    if not (rewards.is_contiguous() and values.is_contiguous() and cu_seqlens.is_contiguous()
+            and bootstrap.is_contiguous()):
+        _lib.require_contiguous(rewards=rewards, values=values, cu_seqlens=cu_seqlens, bootstrap=bootstrap)
     if not (rewards.dim() == values.dim() == cu_seqlens.dim() == 1):
         raise RuntimeError("rewards, values and cu_seqlens must be 1-D")
-    batch = cu_seqlens.numel() - 1
+    batch = cu_seqlens.shape[0] - 1
     total = rewards.shape[0]
     if bootstrap.shape != (batch,):
         raise RuntimeError(f"bootstrap must have shape ({batch},)")
@@ -544,18 +554,35 @@ def _raw_gae_1d_nolp_misalign(
     # The reference zero-fills its outputs (gae.cu:53-54) and then asserts that cu_seqlens covers
     # [0, total) (gae.cu:48-49), so every element is overwritten; zero-filling 2 x 4 B/token first
     # would add 50% to the kernel's HBM traffic. Tokens outside [cu[0], cu[-1]) are undefined here.
-    adv = torch.empty_like(rewards)
-    ret = torch.empty_like(rewards)
-    ws_bytes = lib.b200rl_gae_workspace_bytes(batch, total)
-    ws = _lib.workspace(ws_bytes, dev)
+    # Eager mode: adv and ret are the two rows of ONE allocation (row pitch a multiple of 16 bytes,
+    # which the vectorised SCAN path wants); the custom op (compiled graphs) must not return
+    # tensors that share storage and allocates them separately. Workspace size cached per shape.
+    if one_allocation:
+        Tp = (total + 3) & ~3
+        out = torch.empty((2, Tp), dtype=torch.float32, device=dev)
+        adv, ret = (out[0], out[1]) if Tp == total else (out[0, :total], out[1, :total])
+        p_adv, p_ret = c_void_p(out.data_ptr()), c_void_p(out.data_ptr() + Tp * 4)
+    else:
+        adv, ret = torch.empty_like(rewards), torch.empty_like(rewards)
+        p_adv, p_ret = ptr(adv), ptr(ret)
+    key = (batch, total)
+    ws_bytes = _GAE_WS_BYTES.get(key)
+    if ws_bytes is None:
+        if len(_GAE_WS_BYTES) > 4096:
+            _GAE_WS_BYTES.clear()
+        ws_bytes = _GAE_WS_BYTES[key] = max(int(lib.b200rl_gae_workspace_bytes(batch, total)), 256)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     with _on(dev):
         rc = lib.b200rl_gae_1d_nolp_misalign(
-            ptr(rewards), ptr(values), ptr(cu_seqlens), ptr(bootstrap), ptr(adv), ptr(ret),
-            batch, total, float(gamma), float(lam), int(mode), ptr(ws), ws.numel(),
+            ptr(rewards), ptr(values), ptr(cu_seqlens), ptr(bootstrap), p_adv, p_ret,
+            batch, total, float(gamma), float(lam), int(mode), ptr(ws), ws_bytes,
             stream_handle(dev),
         )
     check(rc, "b200rl_gae_1d_nolp_misalign")
     return adv, ret
+
+
+_GAE_WS_BYTES: dict = {}
 
 
 gae_1d_nolp_misalign_op = torch.library.custom_op("b200rl::gae_1d_nolp_misalign", _raw_gae_1d_nolp_misalign, mutates_args=())
@@ -568,7 +595,7 @@ def _(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode):
 
 def gae_1d_nolp_misalign(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode):
     if _eager():
-        return _raw_gae_1d_nolp_misalign(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode)
+        return _gae_launch(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode, True)
     return gae_1d_nolp_misalign_op(rewards, values, cu_seqlens, bootstrap, gamma, lam, mode)
 
 
