@@ -72,14 +72,22 @@ def run(dev, rank, world, T=4096, V=151936, group=None):
     g2 = torch.randn(T, generator=gen, device=dev) * 0.1
     res = dict(tp=world, T=T, V=V)
     res["all_gather"] = _one(dev, rank, world, T, V, group, full, labels, g1, g2)
+    # the peer-memory transport is optional (it needs CUDA IPC between the ranks): when it cannot be
+    # SET UP the entry says so and parity rests on the all-gather path; once set up, a wrong result
+    # or a timed-out wait fails the check like any other
+    ex = None
     try:
         ex = mcore_functional.enable_peer_exchange(group, max_tokens=max(T, 256))
+    except Exception as e:
+        res["peer_stores"] = dict(available=False, error=repr(e)[:300])
+    if ex is not None:
         res["peer_stores"] = _one(dev, rank, world, T, V, group, full, labels, g1, g2)
-        ex.check()
+        try:
+            ex.check()
+        except Exception as e:
+            res["peer_stores"].update(ok=False, error=repr(e)[:300])
         mcore_functional.disable_peer_exchange(group)
-    except Exception as e:  # a box without peer access keeps the all-gather path
-        res["peer_stores"] = dict(ok=False, error=repr(e)[:300])
-    res["ok"] = bool(res["all_gather"]["ok"] and res["peer_stores"].get("ok"))
+    res["ok"] = bool(res["all_gather"]["ok"] and res["peer_stores"].get("ok", not res["peer_stores"].get("available", True)))
     # headline numbers of the entry = the faster transport
     best = min((r for r in (res["all_gather"], res["peer_stores"]) if "fwd_bwd_ms" in r), key=lambda r: r["fwd_bwd_ms"])
     res.update(max_abs_err=best["max_abs_err"], fwd_bwd_ms=best["fwd_bwd_ms"], tokens_per_s=best["tokens_per_s"],
