@@ -19,6 +19,10 @@
 #include "logprob_common.cuh"
 #include "ppo_math.cuh"
 
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+
 namespace b200rl {
 namespace {
 
@@ -36,21 +40,32 @@ using namespace lp;
 #ifndef B200RL_FUSED_SKEW
 #define B200RL_FUSED_SKEW 0
 #endif
+#ifndef B200RL_FUSED_PAIR_DEFAULT
+#define B200RL_FUSED_PAIR_DEFAULT 1
+#endif
+#ifndef B200RL_FUSED_PAIR_DELAY_DEFAULT
+#define B200RL_FUSED_PAIR_DELAY_DEFAULT 8000
+#endif
 constexpr int kFusedWarps = B200RL_FUSED_WARPS, kFusedStages = B200RL_FUSED_STAGES;
 constexpr bool kFusedSkew = B200RL_FUSED_SKEW != 0;
 
-template <int WARPS, int STAGES>
+// G = rows a CTA works on at once: 1 (all warps on one row) or 2 (pair mode, below)
+template <int WARPS, int STAGES, int G = 1>
 struct FusedSmem {
   static constexpr int kData = WARPS * STAGES * kChunkBytes;
   static constexpr int kBarOff = kData;
-  static constexpr int kPartOff = kBarOff + WARPS * STAGES * 8;   // [2][5][WARPS] float
-  static constexpr int kTokOff = kPartOff + 2 * 5 * WARPS * 4;    // [2][8] float: xy,prox,old,adv,mask
-  static constexpr int kBwdOff = kTokOff + 2 * 8 * 4;             // [2][4]: nlse2, A0, lab_add, lvec*8+lsub
-  static constexpr int kSyncOff = kBwdOff + 2 * 4 * 4;            // cnt[2], ready[2] int
-  static constexpr int kSumOff = (kSyncOff + 4 * 4 + 7) & ~7;     // double sum, double count
-  static constexpr int kBytes = kSumOff + 16;
+  static constexpr int kPartOff = kBarOff + WARPS * STAGES * 8;       // [G][2][WARPS][8] float (G=1: [2][5][WARPS])
+  static constexpr int kTokOff = kPartOff + G * 2 * 8 * WARPS * 4;    // [G][2][8] float: xy,prox,old,adv,mask
+  static constexpr int kBwdOff = kTokOff + G * 2 * 8 * 4;             // [G][2][4]: nlse2, A0, lab_add, label
+  static constexpr int kSyncOff = kBwdOff + G * 2 * 4 * 4;            // [G] x (cnt[2], ready[2]) int
+  static constexpr int kRdyOff = (kSyncOff + G * 4 * 4 + 7) & ~7;     // pair mode: [G][2] "constants ready"
+  static constexpr int kArrOff = kRdyOff + G * 2 * 8;                 //            [G][2] "row statistics in"
+  static constexpr int kSumOff = kArrOff + G * 2 * 8;                 // [G] x (double sum, double count)
+  static constexpr int kBytes = kSumOff + G * 16;
+  static_assert(kPartOff % 16 == 0 && kBwdOff % 16 == 0, "st.async.v4 targets");
 };
-static_assert(FusedSmem<kFusedWarps, kFusedStages>::kBytes <= 227 * 1024, "fused ring exceeds shared memory");
+static_assert(FusedSmem<kFusedWarps, kFusedStages, 2>::kBytes <= 227 * 1024, "fused ring exceeds shared memory");
+static_assert(kFusedWarps % 2 == 0, "pair mode splits the warps in two groups");
 
 struct FusedParams {
   const void* logits;
@@ -78,6 +93,7 @@ struct FusedParams {
   double* partial;        // [grid][2]
   unsigned int* counter;
   float* loss;            // sum(mask * pg * w) / N  (not multiplied by upstream)
+  int pair_delay_ns;      // pair mode: head start of row stream 0
 };
 
 __global__ void __launch_bounds__(1024)
@@ -102,41 +118,85 @@ mask_count_kernel(const uint8_t* __restrict__ mask, const float* __restrict__ ma
   }
 }
 
-template <int DT, int WARPS, int STAGES, bool MINMAX, bool SKEW>
+// PAIR: the kernel runs as clusters of two CTAs (two SMs) that share TWO row streams. Warps
+// 0..WARPS/2-1 of both CTAs work on the rows of stream 0, the other halves on stream 1, so a row
+// is still cut in WARPS slices and a cluster still has one row per SM in flight (the L2 footprint
+// of the re-read is unchanged) - but while one stream sits in the gap between its two passes
+// (the wait for the slowest slice plus the token's loss math, 11 % of the warp time in the
+// one-row-per-CTA form, profiles/r02_ncu_fused.txt) the warps of the other stream keep the MUFU
+// and issue pipes of BOTH SMs busy. All traffic between the CTAs is st.async into distributed
+// shared memory completing on an mbarrier of the receiving CTA (no cluster-scope fence: the
+// release/acquire form of the same protocol cost a MEMBAR per warp and row, which has to wait for
+// the warp's dlogits stores): each warp sends its slice statistics to CTA 0, where a rotating
+// "finisher" warp of the stream waits for all of them, does the token's loss and sends the four
+// backward constants to both CTAs.
+template <int DT, int WARPS, int STAGES, bool MINMAX, bool SKEW, bool PAIR>
 __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  using L = FusedSmem<WARPS, STAGES>;
+  constexpr int G = PAIR ? 2 : 1;
+  using L = FusedSmem<WARPS, STAGES, G>;
   using E = Elem<DT>;
   constexpr uint32_t kNeutral = E::kNeutralWord;
   constexpr bool ENT = true;
+  static_assert(!(PAIR && SKEW), "pair mode has its own overlap");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* part = reinterpret_cast<float*>(smem + L::kPartOff);
-  float* tok = reinterpret_cast<float*>(smem + L::kTokOff);
-  float* bwdc = reinterpret_cast<float*>(smem + L::kBwdOff);
-  int* cnt = reinterpret_cast<int*>(smem + L::kSyncOff);
+  const uint32_t cr = PAIR ? cluster_ctarank() : 0u;         // CTA within the cluster
+  const int g = PAIR ? warp / (WARPS / 2) : 0;                // row stream of this warp
+  const int seg = PAIR ? (int)cr * (WARPS / 2) + warp % (WARPS / 2) : warp;  // slice of the row
+  const int first_row = PAIR ? (int)(blockIdx.x - cr) + g : (int)blockIdx.x;
+  float* part = reinterpret_cast<float*>(smem + L::kPartOff) + g * 2 * 8 * WARPS;
+  float* tok = reinterpret_cast<float*>(smem + L::kTokOff) + g * 2 * 8;
+  float* bwdc = reinterpret_cast<float*>(smem + L::kBwdOff) + g * 2 * 4;
+  int* cnt = reinterpret_cast<int*>(smem + L::kSyncOff) + g * 4;
   volatile int* ready = cnt + 2;
-  double* cta_acc = reinterpret_cast<double*>(smem + L::kSumOff);
-  if (threadIdx.x < 4) cnt[threadIdx.x] = 0;
+  uint64_t* rdy = reinterpret_cast<uint64_t*>(smem + L::kRdyOff) + g * 2;
+  uint64_t* arr = reinterpret_cast<uint64_t*>(smem + L::kArrOff) + g * 2;
+  double* cta_acc = reinterpret_cast<double*>(smem + L::kSumOff) + g * 2;
+  if (threadIdx.x < 4 * G) reinterpret_cast<int*>(smem + L::kSyncOff)[threadIdx.x] = 0;
   if (threadIdx.x == 0) {
-    cta_acc[0] = 0.0;
-    cta_acc[1] = 0.0;
+    double* acc0 = reinterpret_cast<double*>(smem + L::kSumOff);
+#pragma unroll
+    for (int i = 0; i < 2 * G; i++) acc0[i] = 0.0;
+    if (PAIR) {
+      uint64_t* r0 = reinterpret_cast<uint64_t*>(smem + L::kRdyOff);
+      uint64_t* a0 = reinterpret_cast<uint64_t*>(smem + L::kArrOff);
+#pragma unroll
+      for (int i = 0; i < 2 * G; i++) {
+        mbar_init(&r0[i], 1);          // the finisher's arrive.expect_tx
+        mbar_init(&a0[i], WARPS / 2);  // the stream's warps of CTA 0 (CTA 1's only send bytes)
+      }
+      fence_barrier_init();
+    }
   }
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // nobody touches the other CTA's shared memory before it is set up
 
   const int T = p.T, V = p.V;
   const float scale = p.scale;
   const float up_over_n = (p.upstream ? p.upstream[0] : 1.f) / p.denom[0];
-  const int nrows = (T - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int nrows = first_row < T ? (T - first_row + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   WarpStream<WARPS, STAGES, 2, SKEW> ws;
-  ws.init(p.logits, p.ld * E::kBytes, V / E::kPerVec, nrows, smem + warp * STAGES * kChunkBytes,
-          reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, warp, lane);
+  ws.init_seg(p.logits, p.ld * E::kBytes, V / E::kPerVec, nrows, smem + warp * STAGES * kChunkBytes,
+              reinterpret_cast<uint64_t*>(smem + L::kBarOff) + warp * STAGES, seg, WARPS, first_row,
+              (int)gridDim.x, lane);
+  if (PAIR && g == 1 && p.pair_delay_ns > 0) {
+    // start the second stream out of phase with the first one, so that their gaps do not coincide
+    uint64_t t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    do {
+      __nanosleep(256);
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    } while (t1 - t0 < (uint64_t)p.pair_delay_ns);
+  }
 
   // pass 1 of row-iteration `it` (forward statistics + the token's loss, row from HBM)
   auto pass1 = [&](int it) {
-      const int row = blockIdx.x + it * gridDim.x;
+      const int row = first_row + it * gridDim.x;
       const int slot = it & 1, use = it >> 1;
       // one (rotating) warp fetches the token's scalars early
-      const bool fetch = (it % WARPS) == warp && lane == 0;
+      // (pair mode: the row's finisher, a warp of CTA 0, which then keeps them in registers)
+      const bool finisher = PAIR && cr == 0 && (it % (WARPS / 2)) == seg;
+      const bool fetch = (PAIR ? finisher : (it % WARPS) == seg) && lane == 0;
       float xy = 0.f, t_prox = 0.f, t_old = 0.f, t_adv = 0.f, t_mask = 0.f;
       int t_lab = -1;
       if (fetch) {
@@ -202,37 +262,65 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
           mx = warp_max(E::max_f(S.pmx));
           mn = warp_min(E::min_f(S.pmn));
         }
-        float* q = part + slot * 5 * WARPS;
+        float* q = part + slot * (PAIR ? 8 : 5) * WARPS;
         int old = 0;
-        if (lane == 0) {
-          q[0 * WARPS + warp] = M;
-          q[1 * WARPS + warp] = Ssum;
-          q[2 * WARPS + warp] = Tt;
-          q[3 * WARPS + warp] = mx;
-          q[4 * WARPS + warp] = mn;
-          if (fetch) {
-            float* tk = tok + slot * 8;
-            tk[0] = xy;
-            tk[1] = t_prox;
-            tk[2] = t_old;
-            tk[3] = t_adv;
-            tk[4] = t_mask;
-            tk[5] = __int_as_float(t_lab);
+        bool finish;
+        float Mw = -kSentinel, Sw = 0.f, Tw = 0.f, mxw = -INFINITY, mnw = INFINITY;
+        if (PAIR) {
+          // slice statistics -> CTA 0's part[slot][seg][0..4], counted on its arr[slot]
+          if (lane == 0) {
+            const uint32_t q_c = dsmem_addr(smem_u32(q + seg * 8), 0);
+            const uint32_t arr_c = dsmem_addr(smem_u32(&arr[slot]), 0);
+            st_async_v4(q_c, M, Ssum, Tt, mx, arr_c);
+            st_async_b32(q_c + 16, mn, arr_c);
+            if (finisher) mbar_expect_tx(&arr[slot], WARPS * 20);
+            else if (cr == 0) mbar_arrive(&arr[slot]);
           }
-          __threadfence_block();
-          old = atomicAdd(&cnt[slot], 1);
+          finish = finisher;
+          if (finish) {
+            for (uint32_t polls = 0; !mbar_try_wait(&arr[slot], (uint32_t)use & 1u);)
+              if (++polls > (1u << 24)) __trap();
+            if (lane < WARPS) {
+              const volatile float* vq = q + lane * 8;
+              Mw = vq[0], Sw = vq[1], Tw = vq[2], mxw = vq[3], mnw = vq[4];
+            }
+          }
+        } else {
+          if (lane == 0) {
+            q[0 * WARPS + warp] = M;
+            q[1 * WARPS + warp] = Ssum;
+            q[2 * WARPS + warp] = Tt;
+            q[3 * WARPS + warp] = mx;
+            q[4 * WARPS + warp] = mn;
+            if (fetch) {
+              float* tk = tok + slot * 8;
+              tk[0] = xy;
+              tk[1] = t_prox;
+              tk[2] = t_old;
+              tk[3] = t_adv;
+              tk[4] = t_mask;
+              tk[5] = __int_as_float(t_lab);
+            }
+            __threadfence_block();
+            old = atomicAdd(&cnt[slot], 1);
+          }
+          old = __shfl_sync(0xffffffffu, old, 0);
+          finish = old == WARPS - 1;
+          if (finish) {
+            __threadfence_block();
+            const volatile float* vq = q;
+            if (lane < WARPS) {
+              Mw = vq[0 * WARPS + lane];
+              Sw = vq[1 * WARPS + lane];
+              Tw = vq[2 * WARPS + lane];
+              mxw = vq[3 * WARPS + lane];
+              mnw = vq[4 * WARPS + lane];
+            }
+          }
         }
-        old = __shfl_sync(0xffffffffu, old, 0);
-        if (old == WARPS - 1) {
-          // ---- last warp to arrive: row statistics, the token's loss, the backward constants ----
-          __threadfence_block();
-          const volatile float* vq = q;
-          const bool has = lane < WARPS;
-          const float Mw = has ? vq[0 * WARPS + lane] : -kSentinel;
-          const float Sw = has ? vq[1 * WARPS + lane] : 0.f;
-          const float Tw = has ? vq[2 * WARPS + lane] : 0.f;
-          const float mxw = has ? vq[3 * WARPS + lane] : -INFINITY;
-          const float mnw = has ? vq[4 * WARPS + lane] : INFINITY;
+        if (finish) {
+          // ---- last warp to arrive / the finisher: row statistics, the token's loss, the
+          // backward constants ----
           const float Mr = warp_max(Mw);
           const float dr = Mw - Mr;
           const float fr = ex2_approx(dr);
@@ -244,26 +332,42 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
             mnr = warp_min(mnw);
           }
           if (lane == 0) {
-            cnt[slot] = 0;
-            const volatile float* tk = tok + slot * 8;
-            const float xyr = tk[0], px = tk[1], ol = tk[2], A = tk[3];
-            const bool m = tk[4] != 0.f;
-            const int lab = __float_as_int(tk[5]);
+            float xyr, px, ol, A, mk;
+            int lab;
+            if (PAIR) {
+              xyr = xy, px = t_prox, ol = t_old, A = t_adv, mk = t_mask, lab = t_lab;
+            } else {
+              cnt[slot] = 0;
+              const volatile float* tk = tok + slot * 8;
+              xyr = tk[0], px = tk[1], ol = tk[2], A = tk[3], mk = tk[4];
+              lab = __float_as_int(tk[5]);
+            }
+            const bool m = mk != 0.f;
             const float l2s = log2f(Sr);
             const float lse_nat = (Mr + l2s) * kLn2;
             const float lpv = (fmaf(xyr, scale, -Mr) - l2s) * kLn2;
             const PpoToken k = ppo_token(lpv, px, ol, A, m, p.clip_lo, p.clip_hi, p.c_clip, p.cap);
-            // The other 23 warps of the CTA are waiting for these four numbers: publish them first,
+            // The other warps of the row are waiting for these four numbers: publish them first,
             // write the row's outputs to global memory afterwards (off their critical path).
             // same operation order as ppo_loss_bwd_kernel + logprob_bwd_kernel (bit-identical dlogits)
             const float glp = k.dlogp * up_over_n;
             float* bc = bwdc + slot * 4;
-            bc[0] = -lse_nat * kLog2e;
-            bc[1] = -glp * p.inv_temp;
-            bc[2] = glp * p.inv_temp;
-            bc[3] = __int_as_float(lab);
-            __threadfence_block();
-            ready[slot] = use + 1;
+            if (PAIR) {
+#pragma unroll
+              for (uint32_t r = 0; r < 2; r++) {
+                const uint32_t rdy_c = dsmem_addr(smem_u32(&rdy[slot]), r);
+                mbar_arrive_expect_tx_dsmem(rdy_c, 16);
+                st_async_v4(dsmem_addr(smem_u32(bc), r), -lse_nat * kLog2e, -glp * p.inv_temp,
+                            glp * p.inv_temp, __int_as_float(lab), rdy_c);
+              }
+            } else {
+              bc[0] = -lse_nat * kLog2e;
+              bc[1] = -glp * p.inv_temp;
+              bc[2] = glp * p.inv_temp;
+              bc[3] = __int_as_float(lab);
+              __threadfence_block();
+              ready[slot] = use + 1;
+            }
             p.lse[row] = lse_nat;
             p.logp[row] = lpv;
             if (p.ent) p.ent[row] = kLn2 * (l2s - Tr / Sr);
@@ -284,7 +388,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
             if (p.s_dual_ratio) p.s_dual_ratio[row] = k.dual ? 1.f : 0.f;
             if (p.s_clip_new) p.s_clip_new[row] = k.clip ? lpv : 0.f;
             if (p.s_clip_old) p.s_clip_old[row] = k.clip ? ol : 0.f;
-            if (m) {  // rows of a CTA are finalised strictly in order: a deterministic sum
+            if (m) {  // rows of a stream are finalised strictly in order: a deterministic sum
+              // (pair mode: the finisher is always a warp of CTA 0, and the next row's finisher
+              // passes arr[] only after this warp's own release-arrive for that row)
               cta_acc[0] += (double)k.pgw;
               cta_acc[1] += 1.0;
             }
@@ -295,15 +401,21 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
   };
   // pass 2 of row-iteration `it` (backward, row from L2)
   auto pass2 = [&](int it) {
-    const int row = blockIdx.x + it * gridDim.x;
+    const int row = first_row + it * gridDim.x;
     const int slot = it & 1, use = it >> 1;
       // ---------------- pass 2: backward (row again, from L2) ----------------
-      if (lane == 0) {
-        while (ready[slot] < use + 1) {
+      if (PAIR) {
+        // (a wait of microseconds; the bound turns a lost arrival into an error, not a hung GPU)
+        for (uint32_t polls = 0; !mbar_try_wait(&rdy[slot], (uint32_t)use & 1u);)
+          if (++polls > (1u << 24)) __trap();
+      } else {
+        if (lane == 0) {
+          while (ready[slot] < use + 1) {
+          }
         }
+        __syncwarp();
+        __threadfence_block();
       }
-      __syncwarp();
-      __threadfence_block();
       const volatile float* bc = bwdc + slot * 4;
       const float nlse2 = bc[0], A0 = bc[1], lab_add = bc[2];
       const int lab = __float_as_int(bc[3]);
@@ -356,14 +468,18 @@ __global__ void __launch_bounds__(WARPS * 32, 1) grpo_fused_kernel(const FusedPa
     }
   }
 
-  // ---- loss: per-CTA partial, the last CTA adds them in index order --------------------------
+  // ---- loss: per-stream partial, the last CTA adds them in index order -----------------------
+  // (partial b holds the rows b, b + grid, ... in both modes: the same sums in the same order)
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // every remote update of CTA 0's sums has landed; CTA 1 is done
   __shared__ bool is_last;
+  if (PAIR && cr != 0) return;
   if (threadIdx.x == 0) {
-    p.partial[2 * blockIdx.x] = cta_acc[0];
-    p.partial[2 * blockIdx.x + 1] = cta_acc[1];
+    const double* acc0 = reinterpret_cast<const double*>(smem + L::kSumOff);
+#pragma unroll
+    for (int i = 0; i < 2 * G; i++) p.partial[2 * blockIdx.x + i] = acc0[i];
     __threadfence();
-    is_last = atomicAdd(p.counter, 1u) == gridDim.x - 1;
+    is_last = atomicAdd(p.counter, (unsigned)G) == gridDim.x - G;
   }
   __syncthreads();
   if (is_last && threadIdx.x == 0) {
@@ -421,13 +537,88 @@ int set_smem_once(K kernel, int bytes) {
   return ensure_dynamic_smem(reinterpret_cast<const void*>(kernel), bytes);
 }
 
+// B200RL_FUSED_PAIR=0 selects the one-row-per-CTA form; B200RL_FUSED_PAIR_DELAY_NS the head
+// start of the first row stream (both read once).
+struct PairConfig {
+  bool on;
+  int delay_ns;
+};
+const PairConfig& pair_config() {
+  static const PairConfig c = [] {
+    PairConfig r{B200RL_FUSED_PAIR_DEFAULT != 0, B200RL_FUSED_PAIR_DELAY_DEFAULT};
+    if (const char* e = getenv("B200RL_FUSED_PAIR")) r.on = atoi(e) != 0;
+    if (const char* e = getenv("B200RL_FUSED_PAIR_DELAY_NS")) r.delay_ns = atoi(e);
+    return r;
+  }();
+  return c;
+}
+
+// clusters of two CTAs that can be resident at once on this device (cached per device)
+template <typename K>
+int max_pair_clusters(K kernel, int smem) {
+  static std::mutex mu;
+  static int cached[64];
+  static bool have[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!have[dev]) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * sm_count());
+    cfg.blockDim = dim3(kFusedWarps * 32);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess) {
+      cudaGetLastError();
+      n = 0;
+    }
+    cached[dev] = n;
+    have[dev] = true;
+    if (getenv("B200RL_FUSED_PAIR_VERBOSE")) fprintf(stderr, "b200rl: fused pair mode: %d clusters of 2 fit (device %d, %d SMs)\n", n, dev, sm_count());
+  }
+  return cached[dev];
+}
+
 template <int DT, bool MINMAX>
-int launch_fused(const FusedParams& p, cudaStream_t st) {
-  auto k = grpo_fused_kernel<DT, kFusedWarps, kFusedStages, MINMAX, kFusedSkew>;
-  constexpr int smem = FusedSmem<kFusedWarps, kFusedStages>::kBytes;
+int launch_fused(FusedParams p, cudaStream_t st) {
+  const PairConfig& pc = pair_config();
+  if (pc.on && !kFusedSkew && p.T >= 2) {
+    auto k = grpo_fused_kernel<DT, kFusedWarps, kFusedStages, MINMAX, false, true>;
+    constexpr int smem = FusedSmem<kFusedWarps, kFusedStages, 2>::kBytes;
+    int rc = set_smem_once(k, smem);
+    if (rc) return rc;
+    const int clusters = min(max_pair_clusters(k, smem), min((p.T + 1) / 2, 512));
+    if (clusters > 0) {
+      p.pair_delay_ns = pc.delay_ns;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(2 * clusters);
+      cfg.blockDim = dim3(kFusedWarps * 32);
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = st;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 2;
+      at[0].val.clusterDim.y = 1;
+      at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      B200RL_CUDA(cudaLaunchKernelEx(&cfg, k, p));
+      return check_launch("grpo_fused_kernel (pair)");
+    }
+  }
+  auto k = grpo_fused_kernel<DT, kFusedWarps, kFusedStages, MINMAX, kFusedSkew, false>;
+  constexpr int smem = FusedSmem<kFusedWarps, kFusedStages, 1>::kBytes;
   int rc = set_smem_once(k, smem);
   if (rc) return rc;
   const int grid = min(p.T, min(sm_count(), 1024));
+  p.pair_delay_ns = 0;
   k<<<grid, kFusedWarps * 32, smem, st>>>(p);
   return check_launch("grpo_fused_kernel");
 }

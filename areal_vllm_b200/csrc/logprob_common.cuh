@@ -175,17 +175,26 @@ struct WarpStream {
   __device__ __forceinline__ void init(const void* base, int64_t ld_bytes, int nvec, int nrows,
                                        unsigned char* my_data, uint64_t* my_bar, int warp,
                                        int lane) {
+    init_seg(base, ld_bytes, nvec, nrows, my_data, my_bar, warp, WARPS, (int)blockIdx.x,
+             (int)gridDim.x, lane);
+  }
+
+  // General form: this warp streams slice `seg` of `nsegs` of the rows first_row,
+  // first_row + row_step, ... (`nrows` of them).
+  __device__ __forceinline__ void init_seg(const void* base, int64_t ld_bytes, int nvec, int nrows,
+                                           unsigned char* my_data, uint64_t* my_bar, int seg,
+                                           int nsegs, int first_row, int row_step, int lane) {
     const int R = (nvec + 31) >> 5;
-    const int q = R / WARPS, rem = R % WARPS;
-    const int my_rows = q + (warp < rem ? 1 : 0);
-    sv = (warp * q + min(warp, rem)) * 32;
+    const int q = R / nsegs, rem = R % nsegs;
+    const int my_rows = q + (seg < rem ? 1 : 0);
+    sv = (seg * q + min(seg, rem)) * 32;
     seg_len = max(0, min(my_rows * 32, nvec - sv));
-    row_jump = (int64_t)gridDim.x * ld_bytes - (int64_t)seg_len * 16;
-    p_src = reinterpret_cast<const char*>(base) + (int64_t)blockIdx.x * ld_bytes + (int64_t)sv * 16;
+    row_jump = (int64_t)row_step * ld_bytes - (int64_t)seg_len * 16;
+    p_src = reinterpret_cast<const char*>(base) + (int64_t)first_row * ld_bytes + (int64_t)sv * 16;
     p_left = seg_len;
     p_pass = 0;
     p_rows_left = seg_len > 0 ? nrows : 0;
-    row_stride = (int64_t)gridDim.x * ld_bytes;
+    row_stride = (int64_t)row_step * ld_bytes;
     a_ptr = b_ptr = p_src;
     a_left = nrows;
     a_done = 0;

@@ -178,3 +178,23 @@ def test_fused_second_backward_is_refused(cuda):
     with pytest.raises(RuntimeError, match="already consumed"):
         (loss * 2.0).backward()
     assert torch.equal(xg.grad, first)
+
+
+def test_fused_pair_mode_bit_identical_to_one_row_per_cta(cuda):
+    """The default launch runs clusters of two CTAs sharing two row streams (csrc/grpo_fused.cu,
+    pair mode); B200RL_FUSED_PAIR=0 selects the one-row-per-CTA form. Same arithmetic in the same
+    order: every output of every shape must agree bit for bit (the mode is read once per process,
+    hence the two subprocesses)."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for mode in ("0", "1"):
+        env = dict(os.environ, B200RL_FUSED_PAIR=mode)
+        r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fused_pair_check.py")], env=env,
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout)
+    assert outs[0].count("\n") >= 7 and outs[0] == outs[1]
