@@ -9,14 +9,16 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "areal_vllm_b200", "libb200rl.so")
 WANT = [("logprob_fwd_kernel<0, 24, 2, 1, 1>", "logprob_fwd_kernelILi0ELi24ELi2ELb1ELb1EE"),
         ("logprob_bwd_kernel<0, 0>", "logprob_bwd_kernelILi0ELb0EE"),
-        ("grpo_fused_kernel<0, 24, 2, 1, 0>", "grpo_fused_kernelILi0ELi24ELi2ELb1ELb0EE"),
+        ("grpo_fused_kernel<0, 24, 2, 1, 0, pair=1> (clusters of two CTAs; STAS = st.async into distributed shared memory)",
+         "grpo_fused_kernelILi0ELi24ELi2ELb1ELb0ELb1EE"),
+        ("grpo_fused_kernel<0, 24, 2, 1, 0, pair=0>", "grpo_fused_kernelILi0ELi24ELi2ELb1ELb0ELb0EE"),
         ("gae_pieces_kernel", "gae_pieces_kernel"),
         ("gae_serial_kernel", "gae_serial_kernelE"),
         ("gae_serial_slots_kernel", "gae_serial_slots_kernel"),
         ("interval_copy_kernel (first instance)", "interval_copy_kernel"),
         ("interval_move_kernel (first instance)", "interval_move_kernel")]
 KEY = re.compile(r"\b(UBLKCP|SYNCS|LDGSTS|LDGDEPBAR|MUFU\.\w+|STG\.E\.\w*128|STG\.E\.NA\.128|LDG\.E\.\w*128|LDS\.128|STS\.128|"
-                 r"UTMALDG|UTMASTG|UTCMMA|UTCHMMA|HMMA|LDTM|STTM|F2FP\.\w+|VHMNMX|SHFL\.\w+|ATOM\w*|RED\w*)")
+                 r"STAS\.?\w*|UCGABAR_\w+|MEMBAR\.\w+\.\w+|UTMALDG|UTMASTG|UTCMMA|UTCHMMA|HMMA|LDTM|STTM|F2FP\.\w+|VHMNMX|SHFL\.\w+|ATOM\w*|RED\w*)")
 
 sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
 funcs, cur = collections.OrderedDict(), None
