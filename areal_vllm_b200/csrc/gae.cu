@@ -178,6 +178,174 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
   }
 }
 
+// ============================ SERIAL, team ===================================
+// Few sequences (fewer than ~7 per SM) make the kernel a LATENCY problem: the time is the longest
+// sequence's dependent FMA chain, 4 cycles per token at best, and gae_serial_kernel spends ~10
+// because one warp does everything in turn (deltas -> shared memory, chain, results -> global) and
+// the chain's own 16-byte shared loads/stores sit between its FMAs. Here two warps share a
+// sequence through a ring of 256-token blocks in shared memory: warp 0 loads, forms the deltas
+// (two blocks ahead) and writes finished blocks out; lane 0 of warp 1 does nothing but the chain,
+// with the next 32 deltas already in registers while the current 32 FMAs run, so the FMA pipe of
+// that one lane is the only thing on the critical path. Same operations in the same order as the
+// reference (gae.cu:10-28): same bits. Hand-off: one mbarrier per ring slot and direction.
+constexpr int kTeamSlots = 4;  // ring depth
+constexpr int kTeamLag = 2;    // warp 0 writes block j out after it has produced block j + kTeamLag
+static_assert(kTeamSlots > kTeamLag, "a slot is reused only after its results were written out");
+
+__device__ __forceinline__ void team_wait(uint64_t* bar, uint32_t parity) {
+  // microseconds at most; the bound turns a lost arrival into an error instead of a hung GPU
+  for (uint32_t polls = 0; !mbar_try_wait(bar, parity);)
+    if (++polls > (1u << 26)) __trap();
+}
+
+__global__ void __launch_bounds__(64)
+gae_serial_team_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+                       const int32_t* __restrict__ cu, const uint8_t* __restrict__ boot,
+                       float* __restrict__ adv, float* __restrict__ ret, int batch, float gamma,
+                       float lam) {
+  __shared__ __align__(16) float sd[kTeamSlots][kSerBlk];  // deltas in, advantages out
+  __shared__ __align__(16) float sv[kTeamSlots][kSerBlk];  // values, for ret = adv + v
+  __shared__ uint64_t full[kTeamSlots], done[kTeamSlots];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < kTeamSlots; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&done[s], 1);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const float c = __fmul_rn(gamma, lam);  // ref gae.cu:24 `gamma * lmbda * lastgae`
+  uint32_t gb = 0;  // blocks this team has been through: block g uses slot g % S in phase (g / S) & 1
+  for (int i = blockIdx.x; i < batch; i += gridDim.x) {
+    const int rs = cu[i], re = cu[i + 1];
+    const int n = re - rs;
+    if (n <= 0) continue;
+    const int nb = (n + kSerBlk - 1) / kSerBlk;  // block j = tokens [n - 256 (j+1), n - 256 j)
+    if (w == 0) {
+      // ---------------- producer / writer ----------------
+      const float* rbase = rewards + rs;
+      const float* vbase = values + ((int64_t)rs + i);  // sequence i's values start at cu[i] + i
+      SerBlock Ba, Bb;
+      ser_load(Ba, rbase, vbase, n, lane);
+      // the sequence's last step without bootstrap sees next value 0 (gae.cu:20-21)
+      if (boot[i] == 0 && lane == 31) Ba.vn[kSerPerLane - 1] = 0.f;
+      if (nb > 1) ser_load(Bb, rbase, vbase, n - kSerBlk, lane);
+      auto step = [&](SerBlock& B, int j) {
+        if (j < nb) {
+          const uint32_t g = gb + (uint32_t)j;
+          float* d = sd[g % kTeamSlots];
+          float* v = sv[g % kTeamSlots];
+#pragma unroll
+          for (int k = 0; k < kSerPerLane; k++) {
+            // delta in the reference's contraction: fma(gamma, next_v, r) - v   (gae.cu:22-23)
+            d[32 * k + lane] = __fsub_rn(__fmaf_rn(gamma, B.vn[k], B.r[k]), B.v[k]);
+            v[32 * k + lane] = B.v[k];
+          }
+          if (j + 2 < nb) ser_load(B, rbase, vbase, n - (j + 2) * kSerBlk, lane);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&full[g % kTeamSlots]);
+        }
+        const int jo = j - kTeamLag;
+        if (jo >= 0 && jo < nb) {
+          const uint32_t g = gb + (uint32_t)jo;
+          team_wait(&done[g % kTeamSlots], (g / kTeamSlots) & 1u);
+          const float* d = sd[g % kTeamSlots];
+          const float* v = sv[g % kTeamSlots];
+          const int lo = n - (jo + 1) * kSerBlk;
+          float* ap = adv + rs + lo + lane;
+          float* tp = ret + rs + lo + lane;
+          if (lo >= 0) {
+#pragma unroll
+            for (int k = 0; k < kSerPerLane; k++) {
+              const float A = d[32 * k + lane];
+              ap[32 * k] = A;
+              tp[32 * k] = __fadd_rn(A, v[32 * k + lane]);  // gae.cu:26
+            }
+          } else {
+            const int first = -lo - lane;  // slot 32*k + lane holds a token iff 32*k >= first
+#pragma unroll
+            for (int k = 0; k < kSerPerLane; k++) {
+              if (32 * k >= first) {
+                const float A = d[32 * k + lane];
+                ap[32 * k] = A;
+                tp[32 * k] = __fadd_rn(A, v[32 * k + lane]);
+              }
+            }
+          }
+          __syncwarp();  // every lane has read the slot before this warp writes into it again
+        }
+      };
+      for (int j = 0; j < nb + kTeamLag; j += 2) {
+        step(Ba, j);
+        step(Bb, j + 1);
+      }
+    } else {
+      // ---------------- the chain ----------------
+      float X = 0.f;  // lastgae
+      for (int j = 0; j < nb; j++) {
+        const uint32_t g = gb + (uint32_t)j;
+        team_wait(&full[g % kTeamSlots], (g / kTeamSlots) & 1u);
+        if (lane == 0) {
+          float* d = sd[g % kTeamSlots];
+          const int lo = n - (j + 1) * kSerBlk;
+          if (lo >= 0) {
+            // a whole block: 8 groups of 32 tokens, the next group's 8 vectors are loaded before
+            // the current group's 32 dependent FMAs start
+            float4 cur[8], nxt[8];
+#pragma unroll
+            for (int q4 = 0; q4 < 8; q4++) cur[q4] = *reinterpret_cast<const float4*>(d + kSerBlk - 4 - 4 * q4);
+#pragma unroll
+            for (int grp = 0; grp < kSerBlk / 32; grp++) {
+              const int top = kSerBlk - 32 * grp;  // this group = slots [top - 32, top)
+              if (grp + 1 < kSerBlk / 32) {
+#pragma unroll
+                for (int q4 = 0; q4 < 8; q4++)
+                  nxt[q4] = *reinterpret_cast<const float4*>(d + top - 32 - 4 - 4 * q4);
+              }
+#pragma unroll
+              for (int q4 = 0; q4 < 8; q4++) {
+                cur[q4].w = X = __fmaf_rn(c, X, cur[q4].w);
+                cur[q4].z = X = __fmaf_rn(c, X, cur[q4].z);
+                cur[q4].y = X = __fmaf_rn(c, X, cur[q4].y);
+                cur[q4].x = X = __fmaf_rn(c, X, cur[q4].x);
+              }
+#pragma unroll
+              for (int q4 = 0; q4 < 8; q4++) *reinterpret_cast<float4*>(d + top - 4 - 4 * q4) = cur[q4];
+              if (grp + 1 < kSerBlk / 32) {
+#pragma unroll
+                for (int q4 = 0; q4 < 8; q4++) cur[q4] = nxt[q4];
+              }
+            }
+          } else {
+            // the block that reaches the sequence's start: slots below `skip` hold no token
+            const int skip = -lo;
+            int q = kSerBlk - 1;
+#pragma unroll 1
+            for (; q - 3 >= skip; q -= 4) {
+              float4 t = *reinterpret_cast<const float4*>(d + q - 3);
+              t.w = X = __fmaf_rn(c, X, t.w);
+              t.z = X = __fmaf_rn(c, X, t.z);
+              t.y = X = __fmaf_rn(c, X, t.y);
+              t.x = X = __fmaf_rn(c, X, t.x);
+              *reinterpret_cast<float4*>(d + q - 3) = t;
+            }
+#pragma unroll 1
+            for (; q >= skip; q--) {
+              X = __fmaf_rn(c, X, d[q]);
+              d[q] = X;
+            }
+          }
+          mbar_arrive(&done[g % kTeamSlots]);
+        }
+        __syncwarp();
+      }
+    }
+    gb += (uint32_t)nb;
+  }
+}
+
 // ============================ SERIAL, relay ==================================
 // Same warp-per-sequence walk as gae_serial_kernel, but the chain never touches shared memory:
 // after the coalesced loads the 256 deltas are transposed ONCE (8 scalar stores + 2 16-byte loads
@@ -1377,6 +1545,17 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
     gae_serial_slots_kernel<<<grid, kSlotWarps * 32, kSlotSmem, st>>>(
         rewards, values, cu_seqlens, bootstrap, adv, ret, batch, gamma, lam, ticket);
     return check_launch("gae_serial_slots_kernel");
+  }
+  // team: few long sequences, where the longest chain IS the run time (120 x [1k,16k]: see
+  // profiles/r02_gae_modes.txt)
+  if (mode == B200RL_GAE_SERIAL && !short_seqs && total >= (int64_t)batch * 2 * kSerBlk) mode = B200RL_GAE_SERIAL_TEAM;
+  if (mode == B200RL_GAE_SERIAL_TEAM) {
+    int grid = batch;
+    const int cap = sm_count() * 8;
+    if (grid > cap) grid = cap;
+    gae_serial_team_kernel<<<grid, 64, 0, st>>>(rewards, values, cu_seqlens, bootstrap, adv, ret, batch,
+                                               gamma, lam);
+    return check_launch("gae_serial_team_kernel");
   }
   if (mode == B200RL_GAE_SERIAL_RELAY) {
     int grid = (batch + kSerWarps - 1) / kSerWarps;

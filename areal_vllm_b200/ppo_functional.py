@@ -26,8 +26,9 @@ __all__ = [
 _VALIDATE_DEFAULT = os.environ.get("B200RL_VALIDATE", "0") not in ("", "0")
 
 _MODES = {"auto": _lib.GAE_AUTO, "serial": _lib.GAE_SERIAL, "scan": _lib.GAE_SCAN,
-          # SERIAL chooses among these four by batch size (identical bits); forcing is for tests
-          "serial_warp": 3, "serial_batch8": 4, "serial_batch32": 5, "serial_slots": 6, "serial_relay": 7}
+          # SERIAL chooses among these by batch shape (identical bits); forcing is for tests
+          "serial_warp": 3, "serial_batch8": 4, "serial_batch32": 5, "serial_slots": 6, "serial_relay": 7,
+          "serial_team": 8}
 
 
 def gae_1d_nolp_misalign(

@@ -222,11 +222,13 @@ int b200rl_scale_inplace(void* buf, int dtype, int64_t numel, const float* scale
 #define B200RL_GAE_AUTO 0
 #define B200RL_GAE_SERIAL 1
 #define B200RL_GAE_SCAN 2
-/* SERIAL picks among five kernels by batch shape (same bits from all of them); these force one: */
+/* SERIAL picks among six kernels by batch shape (same bits from all of them); these force one: */
 #define B200RL_GAE_SERIAL_WARP 3    /* one warp per sequence */
 #define B200RL_GAE_SERIAL_BATCH8 4  /* 8 sequences per warp, one chain per lane */
 #define B200RL_GAE_SERIAL_BATCH32 5 /* 32 sequences per warp */
 #define B200RL_GAE_SERIAL_RELAY 7   /* one warp per sequence, chain relayed lane to lane in registers */
+#define B200RL_GAE_SERIAL_TEAM 8    /* two warps per sequence: one feeds and drains a ring of blocks, one
+                                       lane of the other runs the chain (few, long sequences) */
 #define B200RL_GAE_SERIAL_SLOTS 6   /* 8 independent sequence slots per warp, refilled from a ticket
                                        counter in `workspace` (static round-robin without one) */
 size_t b200rl_gae_workspace_bytes(int32_t batch, int64_t total);

@@ -13,7 +13,7 @@ def timeit(fn, iters=8, warm=2):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record(); torch.cuda.synchronize(); ts.append(e0.elapsed_time(e1))
     return float(np.median(ts))
-MODES = {"scan": 2, "warp": 3, "relay": 7, "slots": 6}
+MODES = {"scan": 2, "warp": 3, "relay": 7, "slots": 6, "team": 8}
 def case(B, lo, hi, gl=(1.0, 1.0)):
     rng = np.random.default_rng(B)
     lens = rng.integers(lo, hi + 1, B); total = int(lens.sum())
@@ -32,9 +32,16 @@ def case(B, lo, hi, gl=(1.0, 1.0)):
         ms = timeit(run)
         out.append(f"{name} {ms*1e3:8.1f} us ({16.0*total/ms/1e6/6529.4:5.3f})")
     print(f"B={B:7d} len[{lo},{hi}] tok={total:10d}  " + "  ".join(out))
-for B in (256, 1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072):
-    case(B, 64, 2048)
-for B in (8192, 65536, 500000):
-    case(B, 1, 64)
+if "--small" not in sys.argv:
+    for B in (256, 1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072):
+        case(B, 64, 2048)
+    for B in (8192, 65536, 500000):
+        case(B, 1, 64)
+    case(4096, 1024, 16384)
+# few sequences: the longest chain is the run time (team vs warp)
 case(120, 1024, 16384)
-case(4096, 1024, 16384)
+case(512, 1024, 16384)
+case(1000, 1024, 16384)
+case(16, 64, 2048)
+case(512, 64, 2048)
+case(1000, 512, 1024)

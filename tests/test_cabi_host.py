@@ -389,3 +389,19 @@ def test_vocab_parallel_exchange_gloo_world2():
     for _, _, lp, ent in res:  # both ranks hold the same full-vocabulary answer
         np.testing.assert_allclose(lp, lp64.numpy(), rtol=1e-5, atol=1e-6)
         np.testing.assert_allclose(ent, ent64.numpy(), rtol=1e-5, atol=1e-6)
+
+
+def test_gae_mode_codes_match_the_header():
+    """ppo_functional's mode names carry the integer codes include/b200rl.h defines (the C side
+    switches on them), and every forced SERIAL kernel of the header has a name."""
+    import re
+
+    from areal_vllm_b200 import _lib, ppo_functional as PF
+
+    hdr = open(os.path.join(ROOT, "include", "b200rl.h")).read()
+    codes = {m.group(1).lower(): int(m.group(2)) for m in re.finditer(r"#define\s+B200RL_GAE_(\w+)\s+(\d+)", hdr)}
+    assert codes["auto"] == _lib.GAE_AUTO and codes["serial"] == _lib.GAE_SERIAL and codes["scan"] == _lib.GAE_SCAN
+    assert len(set(codes.values())) == len(codes)
+    for name, code in codes.items():
+        assert PF._MODES[name] == code, name
+    assert set(PF._MODES) == set(codes)

@@ -182,8 +182,9 @@ def test_padded_gae_golden(cuda):
         np.testing.assert_allclose(out.cpu().numpy(), g[f"adv_{k}"], rtol=1e-5, atol=1e-5)
 
 
-@pytest.mark.parametrize("mode", ["serial_batch8", "serial_batch32", "serial_slots", "serial_relay"])
-@pytest.mark.parametrize("B,lo,hi", [(1, 1, 5), (7, 1, 300), (33, 64, 2048), (1000, 1, 130), (4099, 0, 70)])
+@pytest.mark.parametrize("mode", ["serial_batch8", "serial_batch32", "serial_slots", "serial_relay", "serial_team"])
+@pytest.mark.parametrize("B,lo,hi", [(1, 1, 5), (7, 1, 300), (33, 64, 2048), (1000, 1, 130), (4099, 0, 70),
+                                     (5, 250, 1030), (200, 0, 3000)])
 @pytest.mark.parametrize("gl", [(1.0, 1.0), (0.99, 0.95)])
 def test_batched_serial_kernels_bit_identical(mode, B, lo, hi, gl, cuda):
     """The many-sequence serial kernels (one chain per lane) give the same bits as the

@@ -56,15 +56,16 @@ def test_gae_vs_reference_kernel(gl, shape, cuda, ref_gae):
 
 @pytest.mark.parametrize("gl", [(1.0, 1.0), (0.99, 0.95)])
 @pytest.mark.parametrize("shape,kernel", [((2048, 30, 1500), "relay"), ((6000, 64, 700), "relay"),
-                                          ((33000, 1, 60), "slots"), ((20000, 1, 50), "batch8")])
+                                          ((33000, 1, 60), "slots"), ((20000, 1, 50), "batch8"),
+                                          ((120, 1024, 16384), "team"), ((512, 300, 9000), "team")])
 def test_gae_large_batches_vs_reference_kernel(gl, shape, kernel, cuda, ref_gae):
-    """Batch shapes that SERIAL dispatches to the relay / slots / batched kernels (gae.cu's dispatch
+    """Batch shapes that SERIAL dispatches to the relay / slots / batched / team kernels (gae.cu's dispatch
     comment), and each of those kernels forced, against the reference kernel: same bits."""
     from areal_vllm_b200 import ppo_functional as PF
 
     r, v, cu, b = _gae_inputs(*shape, seed=37, cuda=cuda)
     a_ref, r_ref = ref_gae.gae_1d_nolp_misalign(r, v, cu, b, gl[0], gl[1])
-    for mode in ("serial", "serial_relay", "serial_slots"):
+    for mode in ("serial", "serial_relay", "serial_slots", "serial_team"):
         a, t = PF.gae_1d_nolp_misalign(r, v, cu, b, gl[0], gl[1], mode=mode)
         assert torch.equal(a, a_ref) and torch.equal(t, r_ref), (mode, kernel)
 
