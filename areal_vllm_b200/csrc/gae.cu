@@ -192,6 +192,9 @@ constexpr int kTeamSlots = 4;  // ring depth
 constexpr int kTeamLag = 2;    // warp 0 writes block j out after it has produced block j + kTeamLag
 static_assert(kTeamSlots > kTeamLag, "a slot is reused only after its results were written out");
 
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w));
+}
 __device__ __forceinline__ void team_wait(uint64_t* bar, uint32_t parity) {
   // microseconds at most; the bound turns a lost arrival into an error instead of a hung GPU
   for (uint32_t polls = 0; !mbar_try_wait(bar, parity);)
@@ -291,28 +294,35 @@ gae_serial_team_kernel(const float* __restrict__ rewards, const float* __restric
           float* d = sd[g % kTeamSlots];
           const int lo = n - (j + 1) * kSerBlk;
           if (lo >= 0) {
-            // a whole block: 8 groups of 32 tokens, the next group's 8 vectors are loaded before
-            // the current group's 32 dependent FMAs start
-            float4 cur[8], nxt[8];
+            // a whole block: 8 groups of 32 tokens, the next group's 8 vectors are requested before
+            // this group's 32 dependent FMAs. (ptxas interleaves one 16-byte load and one store
+            // per four FMAs and reloads a register right after the store that read it; the chain
+            // runs at ~5.9 instead of 4 cycles per token, most likely that write-after-read wait.)
+            const uint32_t da = smem_u32(d);
+            uint4 cur[8], nxt[8];
 #pragma unroll
-            for (int q4 = 0; q4 < 8; q4++) cur[q4] = *reinterpret_cast<const float4*>(d + kSerBlk - 4 - 4 * q4);
+            for (int q4 = 0; q4 < 8; q4++) cur[q4] = lds128(da + 4u * (kSerBlk - 4 - 4 * q4));
 #pragma unroll
             for (int grp = 0; grp < kSerBlk / 32; grp++) {
               const int top = kSerBlk - 32 * grp;  // this group = slots [top - 32, top)
               if (grp + 1 < kSerBlk / 32) {
 #pragma unroll
-                for (int q4 = 0; q4 < 8; q4++)
-                  nxt[q4] = *reinterpret_cast<const float4*>(d + top - 32 - 4 - 4 * q4);
+                for (int q4 = 0; q4 < 8; q4++) nxt[q4] = lds128(da + 4u * (top - 32 - 4 - 4 * q4));
               }
+              uint4 o[8];
 #pragma unroll
               for (int q4 = 0; q4 < 8; q4++) {
-                cur[q4].w = X = __fmaf_rn(c, X, cur[q4].w);
-                cur[q4].z = X = __fmaf_rn(c, X, cur[q4].z);
-                cur[q4].y = X = __fmaf_rn(c, X, cur[q4].y);
-                cur[q4].x = X = __fmaf_rn(c, X, cur[q4].x);
+                X = __fmaf_rn(c, X, __uint_as_float(cur[q4].w));
+                o[q4].w = __float_as_uint(X);
+                X = __fmaf_rn(c, X, __uint_as_float(cur[q4].z));
+                o[q4].z = __float_as_uint(X);
+                X = __fmaf_rn(c, X, __uint_as_float(cur[q4].y));
+                o[q4].y = __float_as_uint(X);
+                X = __fmaf_rn(c, X, __uint_as_float(cur[q4].x));
+                o[q4].x = __float_as_uint(X);
               }
 #pragma unroll
-              for (int q4 = 0; q4 < 8; q4++) *reinterpret_cast<float4*>(d + top - 4 - 4 * q4) = cur[q4];
+              for (int q4 = 0; q4 < 8; q4++) sts128(da + 4u * (top - 4 - 4 * q4), o[q4]);
               if (grp + 1 < kSerBlk / 32) {
 #pragma unroll
                 for (int q4 = 0; q4 < 8; q4++) cur[q4] = nxt[q4];
@@ -1521,7 +1531,10 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
   //   slots   8 independent chains per warp with ticket refill: >= 32k SHORT sequences (500k x
   //           [1,64]: 84 us vs 218 us warp / 144 us for the 32-per-warp kernel);
   //   batch8  8 sequences per warp in lock step: 16k-32k short sequences (< 64 tokens on average);
-  //   warp    one warp per sequence, chain in lane 0: everything else (few or very long sequences).
+  //   team    two warps per sequence (feeder/writer + chain lane): at most 4 sequences per SM of
+  //           >= 512 tokens on average, where the longest chain is the run time (120 x [1k,16k]:
+  //           55 us vs 86 us warp; 512 x [1k,16k]: 70 vs 88 us; 1000 x [1k,16k]: 113 vs 105 us);
+  //   warp    one warp per sequence, chain in lane 0: everything else.
   const bool short_seqs = total < (int64_t)batch * 64;
   const bool use_slots = mode == B200RL_GAE_SERIAL_SLOTS ||
                          (mode == B200RL_GAE_SERIAL && short_seqs && batch >= 32768);
@@ -1548,7 +1561,8 @@ int b200rl_gae_1d_nolp_misalign(const float* rewards, const float* values,
   }
   // team: few long sequences, where the longest chain IS the run time (120 x [1k,16k]: see
   // profiles/r02_gae_modes.txt)
-  if (mode == B200RL_GAE_SERIAL && !short_seqs && total >= (int64_t)batch * 2 * kSerBlk) mode = B200RL_GAE_SERIAL_TEAM;
+  if (mode == B200RL_GAE_SERIAL && batch <= sm_count() * 4 && total >= (int64_t)batch * 2 * kSerBlk)
+    mode = B200RL_GAE_SERIAL_TEAM;
   if (mode == B200RL_GAE_SERIAL_TEAM) {
     int grid = batch;
     const int cap = sm_count() * 8;
