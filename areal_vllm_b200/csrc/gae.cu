@@ -183,12 +183,13 @@ gae_serial_kernel(const float* __restrict__ rewards, const float* __restrict__ v
 // sequence's dependent FMA chain, 4 cycles per token at best, and gae_serial_kernel spends ~10
 // because one warp does everything in turn (deltas -> shared memory, chain, results -> global) and
 // the chain's own 16-byte shared loads/stores sit between its FMAs. Here two warps share a
-// sequence through a ring of 256-token blocks in shared memory: warp 0 loads, forms the deltas
-// (two blocks ahead) and writes finished blocks out; lane 0 of warp 1 does nothing but the chain,
+// sequence through a ring of 256-token blocks in shared memory: warp 0 loads (four blocks ahead),
+// forms the deltas and writes finished blocks out; lane 0 of warp 1 does nothing but the chain,
 // with the next 32 deltas already in registers while the current 32 FMAs run, so the FMA pipe of
 // that one lane is the only thing on the critical path. Same operations in the same order as the
 // reference (gae.cu:10-28): same bits. Hand-off: one mbarrier per ring slot and direction.
 constexpr int kTeamSlots = 4;  // ring depth
+constexpr int kTeamAhead = 4;  // blocks of global loads in flight (registers of warp 0)
 constexpr int kTeamLag = 2;    // warp 0 writes block j out after it has produced block j + kTeamLag
 static_assert(kTeamSlots > kTeamLag, "a slot is reused only after its results were written out");
 
@@ -230,11 +231,14 @@ gae_serial_team_kernel(const float* __restrict__ rewards, const float* __restric
       // ---------------- producer / writer ----------------
       const float* rbase = rewards + rs;
       const float* vbase = values + ((int64_t)rs + i);  // sequence i's values start at cu[i] + i
-      SerBlock Ba, Bb;
+      // four blocks of loads in flight: the chain needs ~0.5 us per block, DRAM ~1 us
+      SerBlock Ba, Bb, Bc, Bd;
       ser_load(Ba, rbase, vbase, n, lane);
       // the sequence's last step without bootstrap sees next value 0 (gae.cu:20-21)
       if (boot[i] == 0 && lane == 31) Ba.vn[kSerPerLane - 1] = 0.f;
       if (nb > 1) ser_load(Bb, rbase, vbase, n - kSerBlk, lane);
+      if (nb > 2) ser_load(Bc, rbase, vbase, n - 2 * kSerBlk, lane);
+      if (nb > 3) ser_load(Bd, rbase, vbase, n - 3 * kSerBlk, lane);
       auto step = [&](SerBlock& B, int j) {
         if (j < nb) {
           const uint32_t g = gb + (uint32_t)j;
@@ -246,7 +250,7 @@ gae_serial_team_kernel(const float* __restrict__ rewards, const float* __restric
             d[32 * k + lane] = __fsub_rn(__fmaf_rn(gamma, B.vn[k], B.r[k]), B.v[k]);
             v[32 * k + lane] = B.v[k];
           }
-          if (j + 2 < nb) ser_load(B, rbase, vbase, n - (j + 2) * kSerBlk, lane);
+          if (j + kTeamAhead < nb) ser_load(B, rbase, vbase, n - (j + kTeamAhead) * kSerBlk, lane);
           __syncwarp();
           if (lane == 0) mbar_arrive(&full[g % kTeamSlots]);
         }
@@ -280,9 +284,11 @@ gae_serial_team_kernel(const float* __restrict__ rewards, const float* __restric
           __syncwarp();  // every lane has read the slot before this warp writes into it again
         }
       };
-      for (int j = 0; j < nb + kTeamLag; j += 2) {
+      for (int j = 0; j < nb + kTeamLag; j += kTeamAhead) {
         step(Ba, j);
         step(Bb, j + 1);
+        step(Bc, j + 2);
+        step(Bd, j + 3);
       }
     } else {
       // ---------------- the chain ----------------

@@ -441,7 +441,8 @@ def run_extras(dev, peak, compiled_baseline=False):
             ms = timeit(lambda: pkg.ppo_functional.cugae1d_nolp_misalign_func(r, v, cu, b, gamma, lam))
             rec = {"workload": name, "gamma": gamma, "lam": lam, "tokens": total,
                    "kernel": "gae_pieces_kernel (tiled scan)" if gamma * lam <= 0.99 else
-                   ("gae_serial_relay_kernel" if B >= 1024 else "gae_serial_kernel"),
+                   ("gae_serial_relay_kernel" if B >= 1024 else
+                    "gae_serial_team_kernel" if B <= 4 * 148 and total >= 512 * B else "gae_serial_kernel"),
                    "us": ms * 1e3, "tokens_per_s": total / (ms * 1e-3),
                    "hbm_frac_of_measured_peak": 16.0 * total / (ms * 1e-3) / 1e9 / peak}
             if B == 256:  # CPU baseline: C port of pygae1d_nolp_misalign, one thread (the python
