@@ -1,5 +1,5 @@
 import os, sys
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from areal_vllm_b200 import _lib
 dev = torch.device("cuda:0")
@@ -8,7 +8,7 @@ for n in (65536, 1048576):
     cu = torch.tensor([0, n], dtype=torch.int32, device=dev); b = torch.ones(1, dtype=torch.uint8, device=dev)
     adv = torch.empty_like(r); ret = torch.empty_like(r)
     ws = _lib.workspace(_lib.lib.b200rl_gae_workspace_bytes(1, n), dev)
-    for name, m in (("warp", 3), ("ws", 6)):
+    for name, m in (("warp", 3), ("relay", 7), ("team", 8)):
         def run():
             rc = _lib.lib.b200rl_gae_1d_nolp_misalign(_lib.ptr(r), _lib.ptr(v), _lib.ptr(cu), _lib.ptr(b), _lib.ptr(adv), _lib.ptr(ret), 1, n, 1.0, 1.0, m, _lib.ptr(ws), ws.numel(), _lib.stream_handle(dev))
             assert rc == 0

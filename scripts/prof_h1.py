@@ -52,3 +52,16 @@ elif what == "gae":
         a2 = pkg.ppo_functional.gae_1d_nolp_misalign(r, v, cu, b, 1.0, 1.0, mode="serial")
     torch.cuda.synchronize()
     print("ok", total)
+elif what == "gae_team":
+    # few long sequences: the team kernel (the longest chain is the run time)
+    rng = np.random.default_rng(120)
+    B = 120
+    lens = rng.integers(1024, 16385, B)
+    total = int(lens.sum())
+    r = torch.randn(total, device=dev); v = torch.randn(total + B, device=dev)
+    cu = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)).to(dev)
+    b = torch.ones(B, dtype=torch.bool, device=dev)
+    for _ in range(3):
+        a2 = pkg.ppo_functional.gae_1d_nolp_misalign(r, v, cu, b, 1.0, 1.0, mode="serial_team")
+    torch.cuda.synchronize()
+    print("ok", total)

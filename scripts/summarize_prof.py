@@ -77,7 +77,9 @@ if os.path.exists("gpurun_out/launches.csv"):
 for name, note in (("prof_h1", "`python scripts/prof_h1.py 2048 h1` (T=2048 rows x V=151936 bf16 = 622 MB per pass)"),
                    ("prof_fused", "`python scripts/prof_h1.py 2048 fused` (fused GRPO step, T=2048 rows x V=151936 bf16; algorithmic HBM bytes 4*V/token = 1244.7 MB)"),
                    ("prof_interval", "`python scripts/prof_interval.py` (cfg5 lists at 1/2 scale: 3.8e9-element bf16 buffer, 5e4 intervals, 3.8 GB copied per pass; slice, set, fused move)"),
-                   ("prof_gae", "`python scripts/prof_h1.py 0 gae` (65536 sequences of 64-2048 tokens, 69 M tokens)"),):
+                   ("prof_gae", "`python scripts/prof_h1.py 0 gae` (65536 sequences of 64-2048 tokens, 69 M tokens)"),
+                   ("prof_gae_team", "`python scripts/prof_h1.py 0 gae_team` (120 sequences of 1024-16384 tokens, gamma = lambda = 1: "
+                                     "the longest sequence's chain is the run time; static schedule of the chain = 4.0 cycles per token)"),):
     rep = f"gpurun_out/{name}.ncu-rep"
     if os.path.exists(rep):
         full(rep, f"{out_dir}/{tag}_ncu_{name[5:]}.txt", note)
