@@ -15,6 +15,8 @@ WANT = [("logprob_fwd_kernel<0, 24, 2, 1, 1>", "logprob_fwd_kernelILi0ELi24ELi2E
         ("gae_pieces_kernel", "gae_pieces_kernel"),
         ("gae_serial_kernel", "gae_serial_kernelE"),
         ("gae_serial_slots_kernel", "gae_serial_slots_kernel"),
+        ("gae_serial_relay_kernel", "gae_serial_relay_kernel"),
+        ("gae_serial_team_kernel (chain lane: per four tokens 4 FFMA + LDS.128 + STS.128)", "gae_serial_team_kernel"),
         ("interval_copy_kernel (first instance)", "interval_copy_kernel"),
         ("interval_move_kernel (first instance)", "interval_move_kernel")]
 KEY = re.compile(r"\b(UBLKCP|SYNCS|LDGSTS|LDGDEPBAR|MUFU\.\w+|STG\.E\.\w*128|STG\.E\.NA\.128|LDG\.E\.\w*128|LDS\.128|STS\.128|"
