@@ -609,8 +609,11 @@ int launch_fused(FusedParams p, cudaStream_t st) {
       at[0].val.clusterDim.z = 1;
       cfg.attrs = at;
       cfg.numAttrs = 1;
-      B200RL_CUDA(cudaLaunchKernelEx(&cfg, k, p));
-      return check_launch("grpo_fused_kernel (pair)");
+      if (cudaLaunchKernelEx(&cfg, k, p) == cudaSuccess) return check_launch("grpo_fused_kernel (pair)");
+      // A cluster launch this context refuses is not an error of the call: the one-row-per-CTA
+      // form below computes the same bits. (A sticky error from earlier work comes back from that
+      // launch as well, so nothing is hidden.)
+      cudaGetLastError();
     }
   }
   auto k = grpo_fused_kernel<DT, kFusedWarps, kFusedStages, MINMAX, kFusedSkew, false>;
