@@ -213,8 +213,11 @@ int b200rl_scale_inplace(void* buf, int dtype, int64_t numel, const float* scale
  *   adv_t   = delta_t + gamma*lam * adv_{t+1};   ret_t = adv_t + v_t.
  * mode: B200RL_GAE_AUTO picks SERIAL when gamma*lam is so close to 1 that re-associating the
  * fp32 additions would move results by more than the 1e-5 parity bar, else SCAN.
- *   SERIAL — one warp per sequence; the recurrence is evaluated in the reference's order
- *            (bit-identical to the reference CUDA kernel), loads/stores are warp-coalesced.
+ *   SERIAL — the recurrence is evaluated in the reference's order (bit-identical to the reference
+ *            CUDA kernel) with warp-coalesced loads/stores; by batch shape one of: a warp per
+ *            sequence (chain in one lane, or relayed lane to lane in registers), a two-warp team
+ *            per sequence (few long sequences), 8 ticket-fed chains per warp or 8/32 sequences per
+ *            warp in lock step (very many short sequences).
  *   SCAN   — segmented reverse affine scan over fixed tiles of the packed stream with a
  *            decoupled look-back across tiles (long sequences spread over many warps).
  * SCAN needs `workspace` of b200rl_gae_workspace_bytes(); it is cleared by the call itself.
