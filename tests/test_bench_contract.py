@@ -115,3 +115,14 @@ def test_round2_multi_gpu_lines_carry_parity(n):
     assert e["adv_max_abs"] <= 1e-5 and e["loss_rel"] <= 1e-3 and e["g_logp_rel"] <= 1e-3 and e["total_loss_weight"] == 0.0
     s = d["strong_scaling"]
     assert s["scaling"] == "strong" and s["imbalance_max_over_mean_tokens"] <= 1.01
+
+
+def test_round2_summary_matches_the_committed_lines():
+    """profiles/r02_SUMMARY.md is generated from the committed bench lines; it must not drift."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("summarize_bench", os.path.join(ROOT, "scripts", "summarize_bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    with open(os.path.join(ROOT, "profiles", "r02_SUMMARY.md")) as f:
+        assert f.read() == mod.build()
