@@ -1,7 +1,7 @@
 """Drop-in for the loss function of ``areal/engine/sft/lm_engine.py`` (the SFT twin of
 ``grpo_loss_fn``): ``compute_packed_sft_loss(logits, input_)``.
 
-Reference (lm_engine.py:45-86): gather_logprobs over the rolled input ids, masked mean of -logp,
+Reference (lm_engine.py:45-83): gather_logprobs over the rolled input ids, masked mean of -logp,
 a python loop over ``cu_seqlens`` for the per-sequence mean log-prob (one host sync per slice
 bound), and two more full passes over ``[T, V]`` for ``logits.min(-1)`` / ``max(-1)``.
 Here: one streaming pass over the logits yields logp AND the row min/max; one small launch yields
@@ -30,7 +30,7 @@ def _stats_tracker():
 
 
 def compute_packed_sft_loss(logits: torch.Tensor, input_: Dict, stats: Optional[Dict] = None) -> torch.Tensor:
-    """ref areal/engine/sft/lm_engine.py:45-86. ``stats`` (extension): when a dict is passed the
+    """ref areal/engine/sft/lm_engine.py:45-83. ``stats`` (extension): when a dict is passed the
     logged tensors are also stored there (ppl, loss, vocab_min_logits, vocab_max_logits, seqlogp,
     n_valid_tokens); inside AReaL they are registered with ``stats_tracker`` under the
     reference's keys and denominators."""

@@ -177,7 +177,7 @@ def gen_critic_rewards(P):
 
 
 def gen_sft():
-    """compute_packed_sft_loss (lm_engine.py:45-86) incl. what it registers with stats_tracker."""
+    """compute_packed_sft_loss (lm_engine.py:45-83) incl. what it registers with stats_tracker."""
     fn, rec = R.sft_loss_fn()
     gen = torch.Generator().manual_seed(31)
     for k, (B, V, dtype, cu_dtype) in enumerate(

@@ -134,7 +134,7 @@ class _StatsRecorder:
 
 
 def sft_loss_fn():
-    """compute_packed_sft_loss (areal/engine/sft/lm_engine.py:45-86) bound to the real
+    """compute_packed_sft_loss (areal/engine/sft/lm_engine.py:45-83) bound to the real
     gather_logprobs and a recording stats tracker. Returns (fn, recorder)."""
     import torch
 

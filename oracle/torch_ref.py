@@ -283,7 +283,7 @@ def packed_rewards(kl_ctl, clip_reward_value, log_probs, ref_log_probs, reward_s
 
 
 def packed_sft_loss(logits, input_ids, cu_seqlens, loss_mask):
-    """Restates areal/engine/sft/lm_engine.py:45-86 (compute_packed_sft_loss) without the stats
+    """Restates areal/engine/sft/lm_engine.py:45-83 (compute_packed_sft_loss) without the stats
     tracker: returns (loss, dict(seqlogp f64, ppl f32, loss per token, vocab_min/max_logits))."""
     labels = torch.roll(input_ids, shifts=-1, dims=-1)
     lp = torch.nn.functional.log_softmax(logits.float(), dim=-1).gather(-1, labels.unsqueeze(-1)).squeeze(-1)

@@ -405,3 +405,30 @@ def test_gae_mode_codes_match_the_header():
     for name, code in codes.items():
         assert PF._MODES[name] == code, name
     assert set(PF._MODES) == set(codes)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="the reference tree is only present in the build container")
+def test_reference_citations_point_at_existing_lines():
+    """Every `path:line[-line]` citation of a reference file in the header, the docs, the package
+    and the oracle names a file that exists in the reference tree and a range inside it."""
+    pat = re.compile(r"((?:areal|realhf|csrc)/[\w/.\-]+\.(?:py|cu|cpp|h|cuh)):(\d+)(?:-(\d+))?")
+    files = ["include/b200rl.h", "DESIGN.md", "INTEGRATION.md", "BASELINE.md", "README.md"]
+    for sub, exts in (("areal_vllm_b200", (".py",)), ("areal_vllm_b200/csrc", (".cu", ".cuh", ".cpp")),
+                      ("oracle", (".py", ".c"))):
+        files += [os.path.join(sub, f) for f in sorted(os.listdir(os.path.join(ROOT, sub))) if f.endswith(exts)]
+    bad, n = [], 0
+    for fn in files:
+        for m in pat.finditer(open(os.path.join(ROOT, fn)).read()):
+            path, a, b = m.group(1), int(m.group(2)), int(m.group(3) or m.group(2))
+            ref = os.path.join("/root/reference", path)
+            if not os.path.exists(ref):
+                if path.startswith("csrc/") and os.path.exists(os.path.join(ROOT, "areal_vllm_b200", path)):
+                    continue  # one of this repo's own kernels
+                bad.append((fn, m.group(0), "no such file"))
+                continue
+            n += 1
+            with open(ref, errors="ignore") as f:
+                length = sum(1 for _ in f)
+            if a > b or b > length:
+                bad.append((fn, m.group(0), f"file has {length} lines"))
+    assert n > 80 and not bad, bad

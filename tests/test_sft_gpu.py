@@ -1,4 +1,4 @@
-"""compute_packed_sft_loss on the GPU (ref areal/engine/sft/lm_engine.py:45-86) against fixtures
+"""compute_packed_sft_loss on the GPU (ref areal/engine/sft/lm_engine.py:45-83) against fixtures
 made by the real reference (incl. everything it registers with stats_tracker) and against the
 oracle on seeded inputs. Tolerances: loss, per-token loss, perplexity within 1e-3 relative
 (north_star; observed ~1e-6), gradient within one ulp of the logits dtype, row min/max exact."""
