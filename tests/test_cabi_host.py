@@ -432,3 +432,43 @@ def test_reference_citations_point_at_existing_lines():
             if a > b or b > length:
                 bad.append((fn, m.group(0), f"file has {length} lines"))
     assert n > 80 and not bad, bad
+
+
+def test_merge_intervals_properties():
+    """Size-independent properties of merge_intervals against a plain-python statement of the
+    reference loop (interval_op.cpp:4-25): neighbours that touch are joined in the order given,
+    the covered elements and their order do not change, and merging is idempotent."""
+    from hypothesis import given, settings, strategies as st
+
+    from areal_vllm_b200.flatten_param import merge_intervals
+
+    def model(iv):
+        out = []
+        for a, b in iv:
+            if out and out[-1][1] == a:
+                out[-1] = (out[-1][0], b)
+            else:
+                out.append((a, b))
+        return out
+
+    pairs = st.lists(st.tuples(st.integers(0, 40), st.integers(0, 12)).map(lambda t: (t[0], t[0] + t[1])), max_size=60)
+    from oracle import ref_loader
+
+    ref_merge = ref_loader.merge_intervals_ext()  # the reference's own interval_op.cpp, when it was built here
+
+    @settings(max_examples=300, deadline=None)
+    @given(pairs)
+    def check(iv):
+        got = merge_intervals(iv)
+        assert got == model(iv)
+        if ref_merge is not None:
+            assert got == [tuple(x) for x in ref_merge(iv)]
+        assert merge_intervals(got) == got
+        flat = lambda L: [x for a, b in L for x in range(a, b)]
+        assert flat(got) == flat(iv)
+
+    check()
+    # a chain of a million touching intervals collapses into one
+    n = 1_000_000
+    big = [(i, i + 1) for i in range(n)]
+    assert merge_intervals(big) == [(0, n)]
