@@ -207,3 +207,49 @@ def test_gae_2d_oracle_reduces_to_1d():
     a3, t3 = cpu_ref.gae_2d_olp(r, v, done, np.array([10], np.int32), cu, np.array([True]), 0.99, 0.95)
     assert a3[0, 9] == 0.0 and t3[0, 9] == v[0, 9]
     assert np.array_equal(a3[0, 10:], a2[0, 10:]) and np.array_equal(a3[1:], a2[1:])
+
+
+def test_oracle_properties_on_random_ragged_inputs():
+    """Size-independent properties of the oracle itself on seeded random inputs (empty sequences,
+    single tokens, every bootstrap pattern; empty and touching intervals): the C statement of the
+    reference kernel, the python-loop statement and the float64 statement agree; GAE is linear in
+    (rewards, values); slice -> set -> slice is the identity on the covered elements."""
+    rng = np.random.default_rng(7)
+    for trial in range(20):
+        B = int(rng.integers(1, 40))
+        lens = rng.integers(0, 70, B)
+        if lens.sum() == 0:
+            lens[0] = 1
+        total = int(lens.sum())
+        cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+        boot = (rng.random(B) < 0.5)
+        gl = [(1.0, 1.0), (0.99, 0.95), (0.9, 0.5)][trial % 3]
+        r1, r2 = (rng.standard_normal(total).astype(np.float32) for _ in range(2))
+        v1, v2 = (rng.standard_normal(total + B).astype(np.float32) for _ in range(2))
+        a_c, t_c = cpu_ref.gae_cuda_order(r1, v1, cu, boot, *gl)
+        a_l, t_l = cpu_ref.gae_py_loops(r1, v1, cu, boot.astype(np.float32), *gl)
+        a_d, t_d = cpu_ref.gae_f64(r1, v1, cu, boot, *gl)
+        np.testing.assert_allclose(a_c, a_l, rtol=1e-5, atol=1e-5)
+        np.testing.assert_allclose(a_c, a_d, rtol=1e-4, atol=1e-4)
+        np.testing.assert_allclose(t_c, t_d, rtol=1e-4, atol=1e-4)
+        # linearity (exact in real arithmetic; fp32 rounding only)
+        a_s, _ = cpu_ref.gae_cuda_order(r1 + r2, v1 + v2, cu, boot, *gl)
+        a_2, _ = cpu_ref.gae_cuda_order(r2, v2, cu, boot, *gl)
+        np.testing.assert_allclose(a_s, a_c + a_2, rtol=1e-4, atol=1e-3)
+        # intervals: disjoint, unsorted, some empty, some touching
+        size = 4000
+        cuts = np.sort(rng.choice(size, 40, replace=False))
+        iv = [(int(cuts[i]), int(cuts[i + 1])) for i in range(0, 38, 2)] + [(int(cuts[5]), int(cuts[5]))]
+        iv += [(int(cuts[39]), int(cuts[39]) + 3)] if cuts[39] + 3 <= size else []
+        rng.shuffle(iv)
+        iv = np.asarray(iv, dtype=np.int64)
+        src = rng.integers(0, 65535, size).astype(np.uint16)
+        packed = cpu_ref.slice_intervals(src, iv)
+        assert packed.size == int((iv[:, 1] - iv[:, 0]).sum())
+        dst = np.full(size, 0xABCD, np.uint16)
+        cpu_ref.set_intervals(packed, dst, iv)
+        covered = np.zeros(size, bool)
+        for a, b in iv:
+            covered[a:b] = True
+        assert np.array_equal(dst[covered], src[covered]) and np.all(dst[~covered] == 0xABCD)
+        assert np.array_equal(cpu_ref.slice_intervals(dst, iv), packed)
