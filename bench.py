@@ -905,7 +905,8 @@ def main_b200rl(args):
                  "hbm_GBps_per_gpu_at_4V": fval / world * 4 * V / 1e9,
                  "frac_of_measured_peak_at_4V": fval / world * 4 * V / 1e9 / peak,
                  "launch": ("one row per CTA" if os.environ.get("B200RL_FUSED_PAIR", "1") in ("0",)
-                            else "pair mode: clusters of two CTAs sharing two row streams"),
+                            else "pair mode: clusters of two CTAs sharing two row streams (the library's default; "
+                                 "it takes the one-row-per-CTA form itself if no cluster fits on the device)"),
                  "note": "each row is read from HBM once (forward statistics) and again from L2 for the "
                          "backward; needs the loss scale before backward(), see INTEGRATION.md"}
 
